@@ -1,0 +1,254 @@
+/*
+ * ps_oracle.c -- CPU restatement of the parameter-server step.  TEST INFRASTRUCTURE ONLY.
+ * PARITY UNPINNED (see ps_oracle.h): the reference holds no implementation of this path
+ * (its only statement about it is k8s-operator.md:6); every function below follows the row of
+ * SURVEY.md section 8(a) named in its comment.
+ *
+ * Build: gcc -O3 -march=x86-64-v3 -ffp-contract=off -fopenmp (oracle/Makefile; v3 so the built .so runs on any host of the pool).
+ * -ffp-contract=off is REQUIRED: one IEEE rounding per written operation.
+ */
+#include "ps_oracle.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+int ps_oracle_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* ---------------------------------------------------------------- synthetic inputs (8d) */
+
+uint64_t ps_hash64(uint64_t seed, uint64_t step, uint64_t worker, uint64_t index) {
+    /* counter packed by three odd multipliers, then the splitmix64 finaliser */
+    uint64_t z = index ^ (seed * 0xD6E8FEB86659FD93ull) ^ (step * 0xA24BAED4963EE407ull) ^
+                 (worker * 0x9FB21C651E98DF25ull);
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+float ps_uniform(uint64_t seed, uint64_t step, uint64_t worker, uint64_t index) {
+    /* top 24 bits -> k * 2^-23 - 1, exact in binary32, range [-1, 1) */
+    uint32_t k = (uint32_t)(ps_hash64(seed, step, worker, index) >> 40);
+    return (float)k * 0x1p-23f - 1.0f;
+}
+
+void ps_fill_uniform(float* dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,
+                     uint64_t first, int threads) {
+    int64_t i;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (i = 0; i < (int64_t)n; ++i) dst[i] = ps_uniform(seed, step, worker, first + (uint64_t)i);
+}
+
+/* ---------------------------------------------------------------- a4: layout */
+
+static uint64_t round_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
+
+uint64_t ps_shard_map(const uint64_t* var_numel, int nvars, int nshards, uint32_t align,
+                      uint64_t* var_offset, uint64_t* slice_begin, uint64_t* slice_end) {
+    uint64_t off = 0, c;
+    int v, s;
+    for (v = 0; v < nvars; ++v) {
+        if (var_offset) var_offset[v] = off;
+        off += round_up(var_numel[v], align);
+    }
+    c = round_up((off + (uint64_t)nshards - 1) / (uint64_t)nshards, align);
+    for (s = 0; s < nshards; ++s) {
+        uint64_t b = (uint64_t)s * c, e = b + c;
+        if (b > off) b = off;
+        if (e > off) e = off;
+        slice_begin[s] = b;
+        slice_end[s] = e;
+    }
+    return off;
+}
+
+void ps_row_range(uint64_t rows, int nshards, int shard, uint64_t* begin, uint64_t* end) {
+    uint64_t q = rows / (uint64_t)nshards, r = rows % (uint64_t)nshards, s = (uint64_t)shard;
+    /* first r shards hold q+1 rows */
+    *begin = s * q + (s < r ? s : r);
+    *end = *begin + q + (s < r ? 1 : 0);
+}
+
+int ps_row_owner(uint64_t rows, int nshards, uint64_t id) {
+    uint64_t q = rows / (uint64_t)nshards, r = rows % (uint64_t)nshards, t = r * (q + 1);
+    if (id < t) return (int)(id / (q + 1));
+    return (int)(r + (id - t) / q);
+}
+
+/* ---------------------------------------------------------------- a6..a8: dense */
+
+#define BLK 512 /* elements per inner block; the per-element operation order never changes */
+
+void ps_dense_sgd(float* p, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
+                  int threads) {
+    int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (b = 0; b < nb; ++b) {
+        float acc[BLK];
+        uint64_t i0 = (uint64_t)b * BLK, len = n - i0 < BLK ? n - i0 : BLK, i;
+        int w;
+        for (i = 0; i < len; ++i) acc[i] = grads[0][i0 + i];
+        for (w = 1; w < W; ++w) {
+            const float* g = grads[w] + i0;
+            for (i = 0; i < len; ++i) acc[i] = acc[i] + g[i];
+        }
+        for (i = 0; i < len; ++i) {
+            float g = acc[i] * inv_w;
+            p[i0 + i] = p[i0 + i] - lr * g;
+        }
+    }
+}
+
+ps_adam_t ps_adam_scalars(double lr, double beta1, double beta2, double eps, uint64_t t) {
+    ps_adam_t a;
+    double b1t = pow(beta1, (double)t), b2t = pow(beta2, (double)t);
+    a.lr_t = (float)(lr * sqrt(1.0 - b2t) / (1.0 - b1t));
+    a.beta1 = (float)beta1;
+    a.beta2 = (float)beta2;
+    a.omb1 = (float)(1.0 - beta1);
+    a.omb2 = (float)(1.0 - beta2);
+    a.eps = (float)eps;
+    return a;
+}
+
+void ps_dense_adam(float* p, float* m, float* v, const float* const* grads, int W, uint64_t n,
+                   float inv_w, const ps_adam_t* a, int threads) {
+    const float lr_t = a->lr_t, b1 = a->beta1, b2 = a->beta2, o1 = a->omb1, o2 = a->omb2,
+                eps = a->eps;
+    int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (b = 0; b < nb; ++b) {
+        float acc[BLK];
+        uint64_t i0 = (uint64_t)b * BLK, len = n - i0 < BLK ? n - i0 : BLK, i;
+        int w;
+        for (i = 0; i < len; ++i) acc[i] = grads[0][i0 + i];
+        for (w = 1; w < W; ++w) {
+            const float* g = grads[w] + i0;
+            for (i = 0; i < len; ++i) acc[i] = acc[i] + g[i];
+        }
+        for (i = 0; i < len; ++i) {
+            float g = acc[i] * inv_w;
+            float mn = b1 * m[i0 + i] + o1 * g;
+            float vn = b2 * v[i0 + i] + o2 * (g * g);
+            m[i0 + i] = mn;
+            v[i0 + i] = vn;
+            p[i0 + i] = p[i0 + i] - (lr_t * mn) / (sqrtf(vn) + eps);
+        }
+    }
+}
+
+/* ---------------------------------------------------------------- a10: gather */
+
+void ps_gather(float* out, const float* table, const int64_t* ids, uint64_t n, int dim,
+               int64_t row_base) {
+    uint64_t k;
+    for (k = 0; k < n; ++k)
+        memcpy(out + k * (uint64_t)dim, table + (uint64_t)(ids[k] - row_base) * (uint64_t)dim,
+               sizeof(float) * (size_t)dim);
+}
+
+/* ---------------------------------------------------------------- a11: bucket, sort, segment */
+
+void ps_bucket_by_owner(const int64_t* ids, uint64_t n, uint64_t rows, int nshards,
+                        uint32_t* perm, uint64_t* bucket_offset) {
+    uint64_t k;
+    int s;
+    uint64_t* cursor = (uint64_t*)calloc((size_t)nshards + 1, sizeof(uint64_t));
+    for (k = 0; k < n; ++k) cursor[ps_row_owner(rows, nshards, (uint64_t)ids[k]) + 1]++;
+    for (s = 0; s < nshards; ++s) cursor[s + 1] += cursor[s];
+    memcpy(bucket_offset, cursor, ((size_t)nshards + 1) * sizeof(uint64_t));
+    for (k = 0; k < n; ++k) perm[cursor[ps_row_owner(rows, nshards, (uint64_t)ids[k])]++] = (uint32_t)k;
+    free(cursor);
+}
+
+typedef struct {
+    int64_t id;
+    uint32_t src;
+} keyed_t;
+
+static int keyed_cmp(const void* a, const void* b) {
+    const keyed_t *x = (const keyed_t*)a, *y = (const keyed_t*)b;
+    if (x->id != y->id) return x->id < y->id ? -1 : 1;
+    if (x->src != y->src) return x->src < y->src ? -1 : 1; /* stability: (worker, position) */
+    return 0;
+}
+
+uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, uint32_t* perm,
+                         int32_t* seg_id, int64_t* unique_ids, uint32_t* seg_offset) {
+    uint64_t k, nu = 0;
+    keyed_t* a;
+    if (n == 0) {
+        if (seg_offset) seg_offset[0] = 0;
+        return 0;
+    }
+    a = (keyed_t*)malloc(n * sizeof(keyed_t));
+    for (k = 0; k < n; ++k) {
+        a[k].id = ids[k];
+        a[k].src = (uint32_t)k;
+    }
+    qsort(a, n, sizeof(keyed_t), keyed_cmp);
+    for (k = 0; k < n; ++k) {
+        if (k == 0 || a[k].id != a[k - 1].id) {
+            unique_ids[nu] = a[k].id;
+            seg_offset[nu] = (uint32_t)k;
+            ++nu;
+        }
+        sorted_ids[k] = a[k].id;
+        perm[k] = a[k].src;
+        seg_id[k] = (int32_t)(nu - 1);
+    }
+    seg_offset[nu] = (uint32_t)n;
+    free(a);
+    return nu;
+}
+
+/* ---------------------------------------------------------------- a12: segmented apply */
+
+void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* grad_rows,
+                         const uint32_t* perm, const int64_t* unique_ids,
+                         const uint32_t* seg_offset, uint64_t n_unique, float inv_w, float lr) {
+    uint64_t u;
+    int d;
+    for (u = 0; u < n_unique; ++u) {
+        float* row = table + (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+        for (d = 0; d < dim; ++d) {
+            uint32_t j = seg_offset[u];
+            float acc = grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d], g;
+            for (++j; j < seg_offset[u + 1]; ++j)
+                acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
+            g = acc * inv_w;
+            row[d] = row[d] - lr * g;
+        }
+    }
+}
+
+void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_base,
+                             const float* grad_rows, const uint32_t* perm,
+                             const int64_t* unique_ids, const uint32_t* seg_offset,
+                             uint64_t n_unique, float inv_w, float lr) {
+    uint64_t u;
+    int d;
+    for (u = 0; u < n_unique; ++u) {
+        uint64_t base = (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+        for (d = 0; d < dim; ++d) {
+            uint32_t j = seg_offset[u];
+            float acc = grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d], g, an;
+            for (++j; j < seg_offset[u + 1]; ++j)
+                acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
+            g = acc * inv_w;
+            an = accum[base + d] + g * g;
+            accum[base + d] = an;
+            table[base + d] = table[base + d] - (lr * g) / sqrtf(an);
+        }
+    }
+}
