@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py -- PS steps/sec and aggregate+apply HBM GB/s (BASELINE.json `metric`).
+
+A step = push + aggregate + apply + pull of one synthetic batch of gradients through the dense PS
+path.  Workload = BASELINE.json configs[1] (dense MLP, 100 685 824 fp32 params, Adam): at N=1
+exactly 2 PS shards + 4 workers on one GPU; at N GPUs the same per-GPU density (2N shards, 4N
+workers), i.e. weak scaling, one process per GPU, no host in the data path.
+
+  value   worker-steps/s = W x synchronous PS steps/s, gradients resident in HBM (whole job)
+  e2e     the same through ParameterServer.step_host with HOST buffers: H2D of every gradient
+          and D2H of the pulled parameters inside the timed region
+  roofline  the aggregate+apply kernel against the measured HBM copy peak
+  cpu_baseline / --impl reference  the CPU oracle (a SUBSTITUTE reference: the upstream repo is
+          documentation only) on the box's host cores, all threads
+
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FALLBACK_HBM_GBS = 6650.0  # B200_PROFILING.md, used only if MEASURED_PEAKS.json is absent
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200ps", choices=["b200ps", "reference"])
+    ap.add_argument("--workload", default="c1", choices=["c0", "c1", "c3"])
+    ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps, capped at 30")
+    return ap.parse_args()
+
+
+def workload(name: str, n_gpus: int):
+    """(label, variable sizes, S, W, optimizer) -- per-GPU density held fixed as N grows."""
+    from b200ps import synth
+
+    if name == "c1":
+        return ("C1 dense MLP 1024-8192-8192-2048-4096, 100685824 fp32 params, Adam, "
+                f"{2 * n_gpus} PS shards + {4 * n_gpus} workers", synth.mlp_c1_variables(), 2 * n_gpus, 4 * n_gpus, "adam")
+    if name == "c3":
+        return (f"C3 ResNet-50-sized set, 25557032 params in 161 variables, Adam, {n_gpus} shards + {n_gpus} workers",
+                synth.resnet50_c3_variables(), n_gpus, n_gpus, "adam")
+    return (f"C0 linear regression 1M params, SGD, {n_gpus} PS + {2 * n_gpus} workers", synth.linreg_c0_variables(),
+            n_gpus, 2 * n_gpus, "sgd")
+
+
+def hbm_peak():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, device_index: int):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.err = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            import torch
+
+            try:
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(device_index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # no NVML: report it, do not fake numbers
+            self.nv, self.err = None, repr(e)
+
+    def run(self):
+        if not self.nv:
+            return
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for b, name in self.REASONS.items():
+                    if bits & b:
+                        self.reasons.add(name)
+            except Exception as e:
+                self.err = repr(e)
+                return
+            time.sleep(0.005)
+
+    def finish(self):
+        self._stop.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        out = {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+               "samples": len(s)}
+        if self.err:
+            out["error"] = self.err
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+def cpu_run(label, sizes, S, W, opt, steps, warmup, seconds=None):
+    """The oracle (oracle/ps_oracle.c, OpenMP, all host threads) on the same workload.
+    Returns (worker_steps_per_s, steps_done, ms_per_step, threads, algorithmic GB/s)."""
+    import numpy as np
+
+    from oracle import c_oracle as O, np_oracle
+
+    nt = O.max_threads()
+    P, _, slices = np_oracle.shard_map(sizes, S, 1024)
+    p = O.fill_uniform(P, 1, 0, 0, threads=nt)
+    m, v = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    g = [O.fill_uniform(P, 2, 1, w, threads=nt) for w in range(W)]
+
+    def one(t):
+        a = O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t)
+        for b, e in slices:
+            if opt == "adam":
+                O.dense_adam(p[b:e], m[b:e], v[b:e], [x[b:e] for x in g], a, threads=nt)
+            else:
+                O.dense_sgd(p[b:e], [x[b:e] for x in g], 0.01, threads=nt)
+
+    t = 0
+    for _ in range(warmup):
+        t += 1
+        one(t)
+    t0 = time.perf_counter()
+    done = 0
+    while done < steps:
+        t += 1
+        one(t)
+        done += 1
+        if seconds is not None and time.perf_counter() - t0 > seconds:
+            break
+    dt = time.perf_counter() - t0
+    bytes_step = (4 * W + (24 if opt == "adam" else 8)) * P
+    return W * done / dt, done, 1e3 * dt / done, nt, bytes_step * done / dt / 1e9
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    label, sizes, S, W, opt = workload(args.workload, args.gpus)
+    val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, args.steps, min(args.warmup, 3))
+    print(json.dumps({
+        "impl": "reference", "metric": "ps_steps_per_sec", "value": round(val, 3), "unit": "worker-steps/s",
+        "n_gpus": args.gpus, "steps": done, "warmup": min(args.warmup, 3), "ms_per_step": round(ms, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt},
+        "ps_steps_per_sec": round(val / W, 3), "algorithmic_GBps": round(gbs, 1),
+        "cpu_baseline": {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
+                         "sample": f"{done} full steps of the workload (every slice, every worker); substitute CPU "
+                                   "reference (oracle/ps_oracle.c, OpenMP) -- the upstream repo has no implementation"},
+        "e2e": {"value": round(val, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    import b200ps
+    from b200ps import kernels as K
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    label, sizes, S, W, opt = workload(args.workload, world)
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport)
+    ps.init_uniform(1)
+    for w in ps.plan.local_workers:
+        K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def reduce_max(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing: `value` and the roofline ----
+    for _ in range(max(args.warmup, 3)):
+        ps.step()
+    sync()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = K.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev[0].record()
+    for i in range(args.steps):
+        if world == 1:
+            kev[i][0].record()
+            ps.step()
+            kev[i][1].record()
+        else:
+            ps.step()
+    ev[1].record()
+    sync()
+    clocks = sampler.finish()
+    launches = K.launch_count() - launches0
+    ms_total = reduce_max(ev[0].elapsed_time(ev[1]))
+    ms_step = ms_total / args.steps
+    steps_per_s = 1e3 / ms_step
+    n_kernels_step = len([L for L in ps.plan.launches if L.end > L.begin])
+    bytes_launch = ps.algorithmic_bytes_per_step() / max(n_kernels_step, 1)
+    if world == 1:
+        k_ms = sum(a.elapsed_time(b) for a, b in kev) / (args.steps * max(n_kernels_step, 1))
+    else:
+        k_ms = None
+    peak, peak_src = hbm_peak()
+    roofline = None
+    if k_ms:
+        ach = bytes_launch / k_ms / 1e6
+        roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                    "traffic": None, "kernel": f"dense_apply_kernel<{opt},W={W}>", "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
+                    "launches_per_step": n_kernels_step}
+
+    # ---- end to end with HOST buffers ----
+    e2e = None
+    if not args.no_e2e:
+        P = ps.plan.P
+        hg = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
+        ho = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
+        for w in hg:
+            hg[w].copy_(ps.grad_buffer(w))
+        sync()
+        n_e2e = args.e2e_steps or min(args.steps, 30)
+        for _ in range(3):
+            ps.step_host(hg, ho)
+        sync()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n_e2e):
+            ps.step_host(hg, ho)
+        b.record()
+        sync()
+        e_ms = reduce_max(a.elapsed_time(b)) / n_e2e
+        # whole-job bytes (every rank moves its own workers' buffers)
+        e2e = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
+               "d2h_bytes_per_step": 4 * P * W, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
+               "ps_steps_per_sec": round(1e3 / e_ms, 3),
+               "api": "b200ps.ParameterServer.step_host (pinned host gradients in, pulled parameters out per worker)"}
+        del hg, ho
+
+    # ---- CPU baseline (rank 0, N = 1 only) ----
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        ps.close()
+        torch.cuda.empty_cache()
+        val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=args.cpu_seconds)
+        cpu = {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
+               "sample": f"{done} full steps ({ms:.1f} ms each, {gbs:.0f} GB/s algorithmic) of the same workload within "
+                         f"{args.cpu_seconds:.0f} s; substitute CPU reference (oracle/ps_oracle.c, OpenMP)"}
+
+    if rank == 0:
+        out = {
+            "metric": "ps_steps_per_sec", "value": round(W * steps_per_s, 3), "unit": "worker-steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 5),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": ps.plan.P,
+                       "transport": args.transport if world > 1 else "local",
+                       "l2": "inputs exceed L2 (per step each GPU streams "
+                             f"{ps.algorithmic_bytes_per_step() / 1e9:.2f} GB >> 126 MB), no flush needed"},
+            "ps_steps_per_sec": round(steps_per_s, 3),
+            "algorithmic_GBps_per_gpu": round(ps.algorithmic_bytes_per_step() / ms_step / 1e6, 1),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,162 @@
+/*
+ * b200ps.h -- C ABI of libb200ps.so: the parameter-server (PS) step of a TFJob on one B200 box.
+ *
+ * What this boundary replaces.  The reference (yph152/tensorflow-k8s) is the notes of a TFJob
+ * operator; it has NO FFI, plugin or kernel interface for the PS data path -- the path lives inside
+ * the TensorFlow containers the operator launches.  Its only statement about the path is the role
+ * model at k8s-operator.md:6 (PS tasks serve parameters, WORKER tasks compute, together a cluster);
+ * the only files that own the operator-facing contract are named, not shown, in images/tf3.PNG
+ * (pkg/apis/tensorflow/v1alpha1/{types,defaults}.go, pkg/apis/tensorflow/validation/validation.go,
+ * pkg/trainer/replicas.go).  Each group below cites the item it stands in for.  A Go operator
+ * would bind these through cgo (INTEGRATION.md shows the stub).
+ *
+ * Conventions
+ *   - plain C99: pointers, sizes, opaque handles; no C++ or torch types.
+ *   - every function returns 0 on success or a negative b200ps_status; the message for the last
+ *     failure on the calling thread is b200ps_last_error().  No abort(), no exit().
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Kernel
+ *     entry points are asynchronous and stream-ordered; device buffers passed in must stay alive
+ *     until the stream reaches that point.
+ *   - pointers named d_* are device pointers on the current device (or peer-mapped pointers of
+ *     another GPU on the same NVSwitch domain); h_* are host pointers.
+ *   - there is no CPU fallback: without a CUDA device the kernel entry points fail.
+ */
+#ifndef B200PS_H
+#define B200PS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PS_MAX_WORKERS 64 /* gradient buffers one launch can fold */
+#define B200PS_MAX_MIRRORS 8  /* extra (peer) copies of the updated slice one launch can write */
+#define B200PS_ALIGN_ELEMS 1024u /* default shard-map alignment, in fp32 elements */
+
+typedef enum {
+    B200PS_OK = 0,
+    B200PS_ERR_INVALID = -1, /* bad argument */
+    B200PS_ERR_PARSE = -2,   /* malformed TFJob / TF_CONFIG JSON */
+    B200PS_ERR_VALIDATION = -3, /* TFJob spec rejected by validation */
+    B200PS_ERR_CUDA = -4,    /* CUDA runtime error (message holds cudaGetErrorString) */
+    B200PS_ERR_RANGE = -5,   /* index / size out of range, buffer too small */
+    B200PS_ERR_STATE = -6    /* call order violated */
+} b200ps_status;
+
+const char* b200ps_last_error(void);
+int b200ps_version(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Contract group: TFJob replica specs in, TF_CONFIG per task out.
+ * Stands in for pkg/apis/tensorflow/v1alpha1/{types,defaults}.go + validation/validation.go
+ * (spec, defaults replicas=1 / tfPort=2222, validation) and pkg/trainer/replicas.go (TF_CONFIG
+ * generation) -- file names in images/tf3.PNG; roles per k8s-operator.md:6.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200ps_cluster b200ps_cluster_t;
+
+/* tfjob_json: a TFJob object as JSON (the launcher converts YAML first).  Accepts the v1alpha1
+ * list form spec.replicaSpecs[{replicas,tfReplicaType,tfPort}] (types MASTER|PS|WORKER) and the
+ * later map form spec.tfReplicaSpecs{Chief|Master|PS|Worker:{replicas,...}}. */
+int b200ps_cluster_from_tfjob(const char* tfjob_json, b200ps_cluster_t** out);
+/* Parses a TF_CONFIG value; task_type receives "ps" | "worker" | "master" | "chief". */
+int b200ps_cluster_from_tf_config(const char* tf_config_json, b200ps_cluster_t** out,
+                                  char* task_type, size_t task_type_cap, int* task_index);
+void b200ps_cluster_destroy(b200ps_cluster_t* c);
+/* number of tasks of a job ("ps", "worker", "master", "chief"); 0 if the job is absent */
+int b200ps_cluster_num_tasks(const b200ps_cluster_t* c, const char* job);
+/* writes "host:port" of one task; returns its length or a negative status */
+int b200ps_cluster_task_address(const b200ps_cluster_t* c, const char* job, int index, char* buf,
+                                size_t cap);
+/* Exact TF_CONFIG string for one task:
+ * {"cluster":{"master":[..],"ps":[..],"worker":[..]},"task":{"type":"worker","index":0},"environment":"cloud"}
+ * (cluster keys in sorted order, no whitespace).  Returns the length or a negative status. */
+int b200ps_tf_config_for(const b200ps_cluster_t* c, const char* job, int index, char* buf,
+                         size_t cap);
+/* Data-path view of the cluster: S = #ps tasks; W = #compute tasks (master/chief first, then
+ * workers -- the master/chief trains too). */
+int b200ps_cluster_num_shards(const b200ps_cluster_t* c);
+int b200ps_cluster_num_workers(const b200ps_cluster_t* c);
+/* compute-task rank of (job, index) in [0, W), or negative if it is not a compute task */
+int b200ps_cluster_worker_rank(const b200ps_cluster_t* c, const char* job, int index);
+/* single-box placement: ps shard s -> GPU s mod G, compute task w -> GPU w mod G */
+int b200ps_placement_gpu(int task_rank, int ngpus);
+
+/* ------------------------------------------------------------------------------------------------
+ * Layout group: PS variable sharding (range partitioning of the flat parameter buffer; TF "div"
+ * partitioning of embedding rows).  Reference: none -- TensorFlow's partitioners inside the user
+ * container; roles per k8s-operator.md:6.  SURVEY.md 8(a) row a4.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200ps_shardmap b200ps_shardmap_t;
+
+int b200ps_shard_map_build(const uint64_t* var_numel, int nvars, int nshards, uint32_t align,
+                           b200ps_shardmap_t** out);
+void b200ps_shard_map_destroy(b200ps_shardmap_t* m);
+uint64_t b200ps_shard_map_total(const b200ps_shardmap_t* m); /* P_pad */
+int b200ps_shard_map_nshards(const b200ps_shardmap_t* m);
+int b200ps_shard_map_nvars(const b200ps_shardmap_t* m);
+int b200ps_shard_map_slice(const b200ps_shardmap_t* m, int shard, uint64_t* begin, uint64_t* end);
+int b200ps_shard_map_var_offset(const b200ps_shardmap_t* m, int var, uint64_t* offset);
+int b200ps_row_range(uint64_t rows, int nshards, int shard, uint64_t* begin, uint64_t* end);
+int b200ps_row_owner(uint64_t rows, int nshards, uint64_t id); /* owner shard or negative */
+
+/* ------------------------------------------------------------------------------------------------
+ * Kernel group (stateless; device pointers; sm_100a).  Reference: none -- TensorFlow's
+ * ApplyGradientDescent / ApplyAdam CPU ops on the PS task and its gRPC tensor transport;
+ * k8s-operator.md:6.  SURVEY.md 8(a) rows a5..a9.
+ *
+ * One launch is push + aggregate + apply + pull for one PS slice of n elements:
+ *   g[i]  = inv_w * (((g_0[i] + g_1[i]) + g_2[i]) + ...)         fixed worker order, W buffers
+ *   SGD:    p[i] -= lr * g[i]
+ *   Adam:   m = b1*m + omb1*g; v = b2*v + omb2*g*g; p -= (lr_t*m) / (sqrt(v) + eps)
+ * then the new p[i] is also written to every d_mirrors[k][i] (the workers' copies on other
+ * GPUs).  d_grads[w] and d_mirrors[k] may be peer-mapped pointers: the loads are the push over
+ * NVLink, the stores the pull.  All arithmetic is fp32 with one IEEE rounding per operation (no
+ * FMA contraction), bit-identical to oracle/ps_oracle.c.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    float lr_t; /* lr * sqrt(1 - beta2^t) / (1 - beta1^t) */
+    float beta1, beta2;
+    float omb1, omb2; /* (float)(1.0 - beta) */
+    float eps;
+} b200ps_adam_t;
+
+/* bias-corrected scalars for step t >= 1, evaluated in double and rounded once */
+int b200ps_adam_scalars(double lr, double beta1, double beta2, double eps, uint64_t t,
+                        b200ps_adam_t* out);
+
+int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, uint64_t n,
+                           float lr, float* const* d_mirrors, int n_mirrors, void* stream);
+int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float* const* d_grads,
+                            int W, uint64_t n, const b200ps_adam_t* opt, float* const* d_mirrors,
+                            int n_mirrors, void* stream);
+/* synthetic inputs: d_dst[i] = uniform[-1,1) from the integer hash of (seed, step, worker,
+ * first+i); identical to ps_fill_uniform of the oracle */
+int b200ps_fill_uniform(float* d_dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,
+                        uint64_t first, void* stream);
+/* launch geometry of the dense kernels: threads per CTA (128..1024), CTAs per SM, float4 per
+ * thread per trip (1, 2 or 4).  0 keeps the current value.  Process-wide; for tuning sweeps. */
+int b200ps_set_dense_tuning(int threads, int ctas_per_sm, int unroll);
+/* number of kernel launches this library has issued in the calling process */
+uint64_t b200ps_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Transport group: buffers other ranks of the box can address.  Reference: none -- TensorFlow's
+ * gRPC tensor transport between the PS and WORKER tasks of k8s-operator.md:6.  One process per
+ * GPU; each rank exports its gradient / parameter arena, every peer maps it, and the step kernel
+ * reads gradients from and writes parameters to the mapped pointers over NVLink (push and pull
+ * fused into the apply).  The handle bytes travel over any host channel (the launcher uses
+ * torch.distributed).
+ * ---------------------------------------------------------------------------------------------- */
+#define B200PS_IPC_HANDLE_BYTES 64
+int b200ps_dev_alloc(size_t bytes, void** d_ptr); /* cudaMalloc on the current device */
+int b200ps_dev_free(void* d_ptr);
+int b200ps_ipc_export(const void* d_ptr, void* handle_out /* B200PS_IPC_HANDLE_BYTES */);
+int b200ps_ipc_open(const void* handle, void** d_ptr); /* maps a peer's allocation */
+int b200ps_ipc_close(void* d_ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PS_H */

@@ -1,0 +1,89 @@
+"""ctypes binding of libb200ps.so -- every symbol include/b200ps.h declares.
+
+There is no fallback: if the library has not been built (`python -c "import __graft_entry__ as g;
+g.build()"` or `make -C tensorflow-k8s_b200/csrc`) importing this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200ps.so")
+
+
+class B200PSError(RuntimeError):
+    """A libb200ps call returned a negative status; `.status` holds it."""
+
+    def __init__(self, status: int, message: str):
+        super().__init__(f"b200ps status {status}: {message}")
+        self.status = status
+
+
+class AdamScalars(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("lr_t", "beta1", "beta2", "omb1", "omb2", "eps")]
+
+
+OK, ERR_INVALID, ERR_PARSE, ERR_VALIDATION, ERR_CUDA, ERR_RANGE, ERR_STATE = 0, -1, -2, -3, -4, -5, -6
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `make -C {os.path.join(_HERE, 'csrc')}` "
+        "(there is no CPU or PyTorch fallback for the parameter-server kernels)")
+
+lib = C.CDLL(LIB_PATH)
+
+_u64, _i32, _u32, _f32, _vp, _cp, _sz = C.c_uint64, C.c_int, C.c_uint32, C.c_float, C.c_void_p, C.c_char_p, C.c_size_t
+_pp = C.POINTER(C.c_void_p)
+
+# name -> (restype, argtypes); mirrors include/b200ps.h one to one (tests/test_abi.py checks it)
+SIGNATURES = {
+    "b200ps_last_error": (_cp, []),
+    "b200ps_version": (_i32, []),
+    "b200ps_cluster_from_tfjob": (_i32, [_cp, _pp]),
+    "b200ps_cluster_from_tf_config": (_i32, [_cp, _pp, _vp, _sz, C.POINTER(_i32)]),
+    "b200ps_cluster_destroy": (None, [_vp]),
+    "b200ps_cluster_num_tasks": (_i32, [_vp, _cp]),
+    "b200ps_cluster_task_address": (_i32, [_vp, _cp, _i32, _vp, _sz]),
+    "b200ps_tf_config_for": (_i32, [_vp, _cp, _i32, _vp, _sz]),
+    "b200ps_cluster_num_shards": (_i32, [_vp]),
+    "b200ps_cluster_num_workers": (_i32, [_vp]),
+    "b200ps_cluster_worker_rank": (_i32, [_vp, _cp, _i32]),
+    "b200ps_placement_gpu": (_i32, [_i32, _i32]),
+    "b200ps_shard_map_build": (_i32, [_vp, _i32, _i32, _u32, _pp]),
+    "b200ps_shard_map_destroy": (None, [_vp]),
+    "b200ps_shard_map_total": (_u64, [_vp]),
+    "b200ps_shard_map_nshards": (_i32, [_vp]),
+    "b200ps_shard_map_nvars": (_i32, [_vp]),
+    "b200ps_shard_map_slice": (_i32, [_vp, _i32, C.POINTER(_u64), C.POINTER(_u64)]),
+    "b200ps_shard_map_var_offset": (_i32, [_vp, _i32, C.POINTER(_u64)]),
+    "b200ps_row_range": (_i32, [_u64, _i32, _i32, C.POINTER(_u64), C.POINTER(_u64)]),
+    "b200ps_row_owner": (_i32, [_u64, _i32, _u64]),
+    "b200ps_adam_scalars": (_i32, [C.c_double] * 4 + [_u64, C.POINTER(AdamScalars)]),
+    "b200ps_dense_apply_sgd": (_i32, [_vp, _vp, _i32, _u64, _f32, _vp, _i32, _vp]),
+    "b200ps_dense_apply_adam": (_i32, [_vp, _vp, _vp, _vp, _i32, _u64, C.POINTER(AdamScalars), _vp, _i32, _vp]),
+    "b200ps_fill_uniform": (_i32, [_vp, _u64, _u64, _u64, _u64, _u64, _vp]),
+    "b200ps_set_dense_tuning": (_i32, [_i32, _i32, _i32]),
+    "b200ps_launch_count": (_u64, []),
+    "b200ps_dev_alloc": (_i32, [_sz, _pp]),
+    "b200ps_dev_free": (_i32, [_vp]),
+    "b200ps_ipc_export": (_i32, [_vp, _vp]),
+    "b200ps_ipc_open": (_i32, [_vp, _pp]),
+    "b200ps_ipc_close": (_i32, [_vp]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(lib, _name)  # AttributeError here = the built library is older than the header
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+def last_error() -> str:
+    return lib.b200ps_last_error().decode("utf-8", "replace")
+
+
+def check(status: int) -> int:
+    """Raise B200PSError for a negative status; pass non-negative values (lengths, counts) through."""
+    if status < 0:
+        raise B200PSError(status, last_error())
+    return status

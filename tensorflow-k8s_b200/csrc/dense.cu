@@ -1,0 +1,363 @@
+// dense.cu -- the dense PS step for one slice: push + aggregate + apply + pull in ONE kernel
+// (include/b200ps.h "Kernel group").
+//
+// Reference: none -- the reference only names the roles (k8s-operator.md:6); in a TFJob the work
+// is TensorFlow's gRPC tensor transport plus its ApplyGradientDescent / ApplyAdam ops on the PS
+// task.  Here one sm_100a kernel streams W gradient buffers (local HBM or NVLink peer memory),
+// folds them in fixed worker order, applies the optimizer to the slice and writes the new
+// parameters to the master copy and to every mirror (the workers' copies on other GPUs).
+//
+// HBM-bound by construction (no contraction anywhere): per element the launch moves
+//   SGD  4W + 8  bytes (W gradient reads, p read, p write)
+//   Adam 4W + 24 bytes (+ m, v read and write)
+// plus 4 bytes per mirror.  No tensor cores, no shared memory (nothing is reused): the design is
+// 128-bit coalesced loads, all of a trip's loads issued before the first use, gradients marked
+// read-once (L1 no-allocate, L2 evict-first) so they do not displace the resident state, and a
+// grid that is a multiple of the SM count.
+//
+// Bit-exactness: every operation is an explicit round-to-nearest intrinsic (__fadd_rn, __fmul_rn,
+// __fdiv_rn, __fsqrt_rn), which the compiler never contracts into FMA, in the operation order of
+// oracle/ps_oracle.c.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+
+#include "common.h"
+#include "cuda_util.h"
+
+namespace b200ps {
+
+std::atomic<uint64_t> g_launches{0};
+
+namespace {
+
+enum { OPT_SGD = 0, OPT_ADAM = 1 };
+
+struct DenseParams {
+    const float* g[B200PS_MAX_WORKERS];
+    float* mirror[B200PS_MAX_MIRRORS];
+    float* p;
+    float* m;
+    float* v;
+    uint64_t n;   // elements in the slice
+    uint64_t n4;  // float4 groups handled by the vector path (0 when a pointer is not 16-B aligned)
+    int W;
+    int n_mirror;
+    float inv_w;
+    float lr;  // SGD: lr.  Adam: lr_t.
+    float beta1, beta2, omb1, omb2, eps;
+};
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+// read-once stream (gradients): non-coherent path, no L1 allocation, first to leave L2
+__device__ __forceinline__ float4 ld_once(const float4* ptr, uint64_t pol) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(ptr), "l"(pol));
+    return r;
+}
+
+// state that this kernel rewrites (p, m, v): coherent load, no L1 allocation, normal L2 priority
+__device__ __forceinline__ float4 ld_state(const float4* ptr) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(ptr));
+    return r;
+}
+
+__device__ __forceinline__ void st_f4(float4* ptr, const float4& v) {
+    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
+    return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
+}
+
+// one element: g = inv_w * sum; optimizer update.  Same operation order as ps_dense_sgd / ps_dense_adam.
+template <int OPT>
+__device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const DenseParams& a) {
+    const float g = __fmul_rn(sum, a.inv_w);
+    if (OPT == OPT_SGD) {
+        p = __fsub_rn(p, __fmul_rn(a.lr, g));
+    } else {
+        m = __fadd_rn(__fmul_rn(a.beta1, m), __fmul_rn(a.omb1, g));
+        v = __fadd_rn(__fmul_rn(a.beta2, v), __fmul_rn(a.omb2, __fmul_rn(g, g)));
+        p = __fsub_rn(p, __fdiv_rn(__fmul_rn(a.lr, m), __fadd_rn(__fsqrt_rn(v), a.eps)));
+    }
+}
+
+template <int OPT>
+__device__ __forceinline__ void apply4(const float4& s, float4& p, float4& m, float4& v, const DenseParams& a) {
+    apply1<OPT>(s.x, p.x, m.x, v.x, a);
+    apply1<OPT>(s.y, p.y, m.y, v.y, a);
+    apply1<OPT>(s.z, p.z, m.z, v.z, a);
+    apply1<OPT>(s.w, p.w, m.w, v.w, a);
+}
+
+// One trip: U float4 groups per stream at i, i+stride, ..., all loads issued before any use.
+// WT > 0: W known at compile time (whole fold unrolled, W*U gradient loads in flight).
+// WT == 0: runtime W, folded four buffers at a time.
+template <int OPT, int WT, int U>
+__device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t stride, uint64_t pol) {
+    float4 acc[U], P[U], M[U], V[U];
+    if (WT > 0) {
+        float4 G[WT > 0 ? WT : 1][U];
+#pragma unroll
+        for (int w = 0; w < WT; ++w)
+#pragma unroll
+            for (int u = 0; u < U; ++u) G[w][u] = ld_once(reinterpret_cast<const float4*>(a.g[w]) + i + u * stride, pol);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
+            if (OPT == OPT_ADAM) {
+                M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
+                V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            acc[u] = G[0][u];
+#pragma unroll
+            for (int w = 1; w < WT; ++w) acc[u] = add4(acc[u], G[w][u]);
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
+            if (OPT == OPT_ADAM) {
+                M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
+                V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
+            }
+            acc[u] = ld_once(reinterpret_cast<const float4*>(a.g[0]) + i + u * stride, pol);
+        }
+        for (int w0 = 1; w0 < a.W; w0 += 4) {
+            float4 G[4][U];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (w0 + c < a.W) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        G[c][u] = ld_once(reinterpret_cast<const float4*>(a.g[w0 + c]) + i + u * stride, pol);
+                }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (w0 + c < a.W) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) acc[u] = add4(acc[u], G[c][u]);
+                }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        apply4<OPT>(acc[u], P[u], M[u], V[u], a);
+        const uint64_t j = i + u * stride;
+        st_f4(reinterpret_cast<float4*>(a.p) + j, P[u]);
+        if (OPT == OPT_ADAM) {
+            st_f4(reinterpret_cast<float4*>(a.m) + j, M[u]);
+            st_f4(reinterpret_cast<float4*>(a.v) + j, V[u]);
+        }
+        for (int k = 0; k < a.n_mirror; ++k) st_f4(reinterpret_cast<float4*>(a.mirror[k]) + j, P[u]);
+    }
+}
+
+template <int OPT, int WT, int U>
+__global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
+    const uint64_t pol = policy_evict_first();
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t i = tid;
+    for (; i + (U - 1) * stride < a.n4; i += U * stride) trip<OPT, WT, U>(a, i, stride, pol);
+    if (U > 1)
+        for (; i < a.n4; i += stride) trip<OPT, WT, 1>(a, i, stride, pol);
+    // scalar tail: n % 4 elements, or the whole slice when a pointer is not 16-byte aligned
+    for (uint64_t j = a.n4 * 4 + tid; j < a.n; j += stride) {
+        float s = a.g[0][j];
+        for (int w = 1; w < a.W; ++w) s = __fadd_rn(s, a.g[w][j]);
+        float p = a.p[j], m = 0.f, v = 0.f;
+        if (OPT == OPT_ADAM) {
+            m = a.m[j];
+            v = a.v[j];
+        }
+        apply1<OPT>(s, p, m, v, a);
+        a.p[j] = p;
+        if (OPT == OPT_ADAM) {
+            a.m[j] = m;
+            a.v[j] = v;
+        }
+        for (int k = 0; k < a.n_mirror; ++k) a.mirror[k][j] = p;
+    }
+}
+
+__device__ __forceinline__ uint64_t hash64(uint64_t key, uint64_t index) {
+    uint64_t z = index ^ key;
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void fill_uniform_kernel(float* __restrict__ dst, uint64_t n, uint64_t key, uint64_t first) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t k = (uint32_t)(hash64(key, first + i) >> 40);
+        dst[i] = __fsub_rn(__fmul_rn((float)k, 0x1p-23f), 1.0f);
+    }
+}
+
+struct Tuning {
+    int threads = 256;
+    int ctas_per_sm = 4;
+    int unroll = 2;
+};
+Tuning g_tuning;
+
+template <int OPT, int WT>
+cudaError_t launch_u(const DenseParams& a, int grid, int threads, int unroll, cudaStream_t st) {
+    switch (unroll) {
+        case 1: dense_apply_kernel<OPT, WT, 1><<<grid, threads, 0, st>>>(a); break;
+        case 4: dense_apply_kernel<OPT, WT, 4><<<grid, threads, 0, st>>>(a); break;
+        default: dense_apply_kernel<OPT, WT, 2><<<grid, threads, 0, st>>>(a); break;
+    }
+    return cudaGetLastError();
+}
+
+template <int OPT>
+cudaError_t launch_w(const DenseParams& a, int grid, int threads, int unroll, cudaStream_t st) {
+    switch (a.W) {
+        case 1: return launch_u<OPT, 1>(a, grid, threads, unroll, st);
+        case 2: return launch_u<OPT, 2>(a, grid, threads, unroll, st);
+        case 4: return launch_u<OPT, 4>(a, grid, threads, unroll, st);
+        case 8: return launch_u<OPT, 8>(a, grid, threads, unroll > 2 ? 2 : unroll, st);
+        default: return launch_u<OPT, 0>(a, grid, threads, unroll > 2 ? 2 : unroll, st);
+    }
+}
+
+int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* const* d_mirrors, void* stream) {
+    B200PS_REQUIRE(a.p && d_grads, B200PS_ERR_INVALID, "null parameter or gradient pointer");
+    B200PS_REQUIRE(a.W >= 1 && a.W <= B200PS_MAX_WORKERS, B200PS_ERR_RANGE, "W = %d is outside 1..%d", a.W,
+                   B200PS_MAX_WORKERS);
+    B200PS_REQUIRE(a.n_mirror >= 0 && a.n_mirror <= B200PS_MAX_MIRRORS, B200PS_ERR_RANGE,
+                   "n_mirrors = %d is outside 0..%d", a.n_mirror, B200PS_MAX_MIRRORS);
+    B200PS_REQUIRE(a.n_mirror == 0 || d_mirrors, B200PS_ERR_INVALID, "null mirror list");
+    if (opt == OPT_ADAM) B200PS_REQUIRE(a.m && a.v, B200PS_ERR_INVALID, "Adam needs m and v");
+    if (a.n == 0) return B200PS_OK;
+
+    uintptr_t bits = (uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v;
+    for (int w = 0; w < a.W; ++w) {
+        B200PS_REQUIRE(d_grads[w], B200PS_ERR_INVALID, "gradient buffer %d is null", w);
+        a.g[w] = d_grads[w];
+        bits |= (uintptr_t)d_grads[w];
+    }
+    for (int k = 0; k < a.n_mirror; ++k) {
+        B200PS_REQUIRE(d_mirrors[k], B200PS_ERR_INVALID, "mirror %d is null", k);
+        a.mirror[k] = d_mirrors[k];
+        bits |= (uintptr_t)d_mirrors[k];
+    }
+    a.n4 = (bits & 15) ? 0 : a.n / 4;
+    a.inv_w = 1.0f / (float)a.W;
+
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const Tuning t = g_tuning;
+    const uint64_t work = a.n4 ? a.n4 : a.n;
+    uint64_t want = (work + (uint64_t)t.threads * (uint64_t)t.unroll - 1) / ((uint64_t)t.threads * (uint64_t)t.unroll);
+    const uint64_t cap = (uint64_t)sms * (uint64_t)t.ctas_per_sm;
+    const int grid = (int)(want < cap ? (want ? want : 1) : cap);
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = opt == OPT_SGD ? launch_w<OPT_SGD>(a, grid, t.threads, t.unroll, st)
+                                   : launch_w<OPT_ADAM>(a, grid, t.threads, t.unroll, st);
+    B200PS_CUDA(e);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+}  // namespace
+}  // namespace b200ps
+
+using namespace b200ps;
+
+extern "C" int b200ps_adam_scalars(double lr, double beta1, double beta2, double eps, uint64_t t, b200ps_adam_t* out) {
+    B200PS_REQUIRE(out, B200PS_ERR_INVALID, "null argument");
+    B200PS_REQUIRE(t >= 1, B200PS_ERR_RANGE, "Adam step t starts at 1");
+    const double b1t = std::pow(beta1, (double)t), b2t = std::pow(beta2, (double)t);
+    out->lr_t = (float)(lr * std::sqrt(1.0 - b2t) / (1.0 - b1t));
+    out->beta1 = (float)beta1;
+    out->beta2 = (float)beta2;
+    out->omb1 = (float)(1.0 - beta1);
+    out->omb2 = (float)(1.0 - beta2);
+    out->eps = (float)eps;
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, uint64_t n, float lr,
+                                      float* const* d_mirrors, int n_mirrors, void* stream) {
+    DenseParams a{};
+    a.p = d_params;
+    a.n = n;
+    a.W = W;
+    a.n_mirror = n_mirrors;
+    a.lr = lr;
+    return dense_apply(OPT_SGD, a, d_grads, d_mirrors, stream);
+}
+
+extern "C" int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float* const* d_grads, int W,
+                                       uint64_t n, const b200ps_adam_t* opt, float* const* d_mirrors, int n_mirrors,
+                                       void* stream) {
+    B200PS_REQUIRE(opt, B200PS_ERR_INVALID, "null optimizer scalars");
+    DenseParams a{};
+    a.p = d_params;
+    a.m = d_m;
+    a.v = d_v;
+    a.n = n;
+    a.W = W;
+    a.n_mirror = n_mirrors;
+    a.lr = opt->lr_t;
+    a.beta1 = opt->beta1;
+    a.beta2 = opt->beta2;
+    a.omb1 = opt->omb1;
+    a.omb2 = opt->omb2;
+    a.eps = opt->eps;
+    return dense_apply(OPT_ADAM, a, d_grads, d_mirrors, stream);
+}
+
+extern "C" int b200ps_fill_uniform(float* d_dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,
+                                   uint64_t first, void* stream) {
+    B200PS_REQUIRE(d_dst || n == 0, B200PS_ERR_INVALID, "null destination");
+    if (n == 0) return B200PS_OK;
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const uint64_t key = (seed * 0xD6E8FEB86659FD93ull) ^ (step * 0xA24BAED4963EE407ull) ^ (worker * 0x9FB21C651E98DF25ull);
+    const uint64_t want = (n + 255) / 256, cap = (uint64_t)sms * 8;
+    fill_uniform_kernel<<<(int)(want < cap ? want : cap), 256, 0, (cudaStream_t)stream>>>(d_dst, n, key, first);
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_set_dense_tuning(int threads, int ctas_per_sm, int unroll) {
+    if (threads) {
+        B200PS_REQUIRE(threads >= 32 && threads <= 1024 && threads % 32 == 0, B200PS_ERR_RANGE,
+                       "threads must be a multiple of 32 in 32..1024");
+        g_tuning.threads = threads;
+    }
+    if (ctas_per_sm) {
+        B200PS_REQUIRE(ctas_per_sm >= 1 && ctas_per_sm <= 32, B200PS_ERR_RANGE, "ctas_per_sm must be in 1..32");
+        g_tuning.ctas_per_sm = ctas_per_sm;
+    }
+    if (unroll) {
+        B200PS_REQUIRE(unroll == 1 || unroll == 2 || unroll == 4, B200PS_ERR_RANGE, "unroll must be 1, 2 or 4");
+        g_tuning.unroll = unroll;
+    }
+    return B200PS_OK;
+}
+
+extern "C" uint64_t b200ps_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

@@ -1,0 +1,326 @@
+"""Host side of the parameter-server step for the tasks placed on THIS process's GPU.
+
+One process per GPU (rank r of G, `torch.distributed`).  The TFJob's PS shards and compute tasks
+are placed on GPUs as SURVEY.md 8(e) says (shard s -> GPU s mod G, worker w -> GPU w mod G); a
+rank owns the gradient buffers of its workers, one replica of the whole parameter vector (what
+its workers read) and the optimizer state of its shards.  The master copy of slice s is the
+slice-s range of its owner's replica.
+
+A step is ONE kernel per local shard (csrc/dense.cu): it loads the W gradient slices straight
+from the buffers of the ranks that hold them (NVLink peer loads = push), folds them in worker
+order, applies the optimizer and stores the new slice into every rank's replica (peer stores =
+pull).  The only other traffic is two stream-ordered barriers (all gradients written / all
+replicas written).  transport="nccl" is the plain library version of the same step
+(reduce-scatter -> apply -> all-gather) kept as the comparison point.
+
+Reference: none -- this is what TensorFlow's PS runtime does inside the containers a TFJob
+launches; the reference states only the roles (k8s-operator.md:6).  torch is plumbing here
+(streams, pinned host memory, torch.distributed); all arithmetic goes through the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ._lib import AdamScalars, check, lib
+from .contract import placement_gpu
+from .layout import ShardMap
+
+IPC_BYTES = 64
+
+
+# --------------------------------------------------------------------------------------------------
+# The plan: pure host logic (no CUDA), so that world_size > 1 can be tested on CPU with gloo.
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class Launch:
+    shard: int
+    begin: int  # element range of the slice in the flat buffer
+    end: int
+    grad_src: List[Tuple[int, int]]  # per worker, in worker order: (rank, arena offset in elements)
+    mirror_ranks: List[int]  # ranks whose replica receives the updated slice (all but this one)
+
+
+@dataclass
+class Plan:
+    rank: int
+    world: int
+    P: int  # padded parameter count
+    W: int
+    S: int
+    local_workers: List[int]
+    local_shards: List[int]
+    arena_elems: int  # replica + one gradient buffer per local worker
+    launches: List[Launch] = field(default_factory=list)
+
+    def grad_offset(self, worker: int) -> Tuple[int, int]:
+        """(rank, element offset in that rank's arena) of a worker's gradient buffer."""
+        r = placement_gpu(worker, self.world)
+        return r, self.P * (1 + worker // self.world)
+
+
+def build_plan(smap: ShardMap, num_workers: int, rank: int, world: int) -> Plan:
+    S, P = smap.nshards, smap.total
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} is outside 0..{world - 1}")
+    if world - 1 > 8:
+        raise ValueError("one launch writes at most 8 peer replicas (B200PS_MAX_MIRRORS)")
+    lw = [w for w in range(num_workers) if placement_gpu(w, world) == rank]
+    ls = [s for s in range(S) if placement_gpu(s, world) == rank]
+    plan = Plan(rank, world, P, num_workers, S, lw, ls, P * (1 + len(lw)))
+    for s in ls:
+        b, e = smap.slice(s)
+        plan.launches.append(Launch(s, b, e, [plan.grad_offset(w) for w in range(num_workers)],
+                                    [r for r in range(world) if r != rank]))
+    return plan
+
+
+# --------------------------------------------------------------------------------------------------
+class _CudaArray:
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+class Arena:
+    """A cudaMalloc'ed fp32 block of this rank, exportable to the other ranks of the box."""
+
+    def __init__(self, nelems: int):
+        p = C.c_void_p()
+        check(lib.b200ps_dev_alloc(nelems * 4, C.byref(p)))
+        self.ptr, self.n = p.value, nelems
+        self.tensor = torch.as_tensor(_CudaArray(self.ptr, nelems), device=torch.device("cuda", torch.cuda.current_device()))
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(IPC_BYTES)
+        check(lib.b200ps_ipc_export(C.c_void_p(self.ptr), buf))
+        return buf.raw
+
+    def free(self):
+        if self.ptr:
+            self.tensor = None
+            check(lib.b200ps_dev_free(C.c_void_p(self.ptr)))
+            self.ptr = 0
+
+
+def _ptrs(vals: Sequence[int]):
+    return (C.c_void_p * max(len(vals), 1))(*vals)
+
+
+class ParameterServer:
+    """The PS tasks and compute-task buffers of one GPU.  See the module docstring."""
+
+    def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
+                 lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
+                 world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20):
+        if optimizer not in ("sgd", "adam"):
+            raise ValueError("optimizer must be 'sgd' or 'adam'")
+        if transport not in ("peer", "nccl"):
+            raise ValueError("transport must be 'peer' or 'nccl'")
+        if not torch.cuda.is_available():
+            raise RuntimeError("b200ps.ParameterServer needs a CUDA device: there is no CPU fallback")
+        self.map = ShardMap(var_numel, num_shards)
+        self.plan = build_plan(self.map, num_workers, rank, world)
+        self.optimizer, self.lr, self.betas, self.eps = optimizer, lr, (beta1, beta2), eps
+        self.rank, self.world, self.group, self.transport = rank, world, group, transport
+        self.chunk = max(1024, chunk_elems // 1024 * 1024)
+        self.t = 0
+        P = self.plan.P
+        self.arena = Arena(self.plan.arena_elems)
+        self.replica = self.arena.tensor[:P]
+        self.grads: Dict[int, torch.Tensor] = {w: self.arena.tensor[P * (1 + i): P * (2 + i)]
+                                               for i, w in enumerate(self.plan.local_workers)}
+        self.state: Dict[int, Tuple[torch.Tensor, torch.Tensor]] = {}
+        if optimizer == "adam":
+            for L in self.plan.launches:
+                n = L.end - L.begin
+                self.state[L.shard] = (torch.zeros(n, dtype=torch.float32, device="cuda"),
+                                       torch.zeros(n, dtype=torch.float32, device="cuda"))
+        self.peer_base: Dict[int, int] = {rank: self.arena.ptr}
+        self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self._s_in, self._s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        if world > 1:
+            self._exchange_handles()
+            if transport == "nccl":
+                self._init_nccl()
+
+    # ---- set-up -------------------------------------------------------------------------------
+    def _exchange_handles(self):
+        import torch.distributed as dist
+
+        blobs: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(blobs, self.arena.export(), group=self.group)
+        for r, blob in enumerate(blobs):
+            if r == self.rank:
+                continue
+            p = C.c_void_p()
+            check(lib.b200ps_ipc_open(C.create_string_buffer(blob, IPC_BYTES), C.byref(p)))
+            self.peer_base[r] = p.value
+
+    def _init_nccl(self):
+        if not (self.plan.S == self.world == self.plan.W):
+            raise ValueError("transport='nccl' is the one-shard-and-one-worker-per-GPU case (S = W = G)")
+        sizes = {e - b for b, e in self.map.slices()}
+        if len(sizes) != 1:
+            raise ValueError("transport='nccl' needs equal slices (P_pad divisible by S * align)")
+        self._gsum = torch.empty(sizes.pop(), dtype=torch.float32, device="cuda")
+
+    def close(self):
+        torch.cuda.synchronize()
+        for r, base in list(self.peer_base.items()):
+            if r != self.rank:
+                lib.b200ps_ipc_close(C.c_void_p(base))
+        self.peer_base = {}
+        self.replica, self.grads = None, {}
+        self.arena.free()
+
+    # ---- parameters ---------------------------------------------------------------------------
+    def init_uniform(self, seed: int = 1):
+        """p[i] = u(seed, 0, 0, i): every rank fills its whole replica with the same values."""
+        check(lib.b200ps_fill_uniform(C.c_void_p(self.arena.ptr), self.plan.P, seed, 0, 0, 0, self._stream()))
+        self._reset_state()
+
+    def init_params(self, host_params: np.ndarray):
+        hp = np.ascontiguousarray(host_params, np.float32)
+        if hp.size != self.plan.P:
+            raise ValueError(f"expected {self.plan.P} padded parameters, got {hp.size}")
+        self.replica.copy_(torch.from_numpy(hp))
+        self._reset_state()
+
+    def _reset_state(self):
+        self.t = 0
+        for m, v in self.state.values():
+            m.zero_()
+            v.zero_()
+
+    # ---- the step -----------------------------------------------------------------------------
+    @staticmethod
+    def _stream() -> C.c_void_p:
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def _barrier(self):
+        """Stream-ordered cross-rank barrier: work queued before it on every rank completes before
+        work queued after it on any rank starts."""
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(self._flag, group=self.group)
+
+    def _opt_scalars(self) -> Optional[AdamScalars]:
+        if self.optimizer != "adam":
+            return None
+        a = AdamScalars()
+        check(lib.b200ps_adam_scalars(self.lr, self.betas[0], self.betas[1], self.eps, self.t, C.byref(a)))
+        return a
+
+    def _launch(self, L: Launch, lo: int, hi: int, a: Optional[AdamScalars]):
+        """One kernel over elements [lo, hi) of slice L (lo/hi in flat-buffer coordinates)."""
+        n = hi - lo
+        g = _ptrs([self.peer_base[r] + 4 * (off + lo) for r, off in L.grad_src])
+        mir = _ptrs([self.peer_base[r] + 4 * lo for r in L.mirror_ranks])
+        p = C.c_void_p(self.arena.ptr + 4 * lo)
+        if a is None:
+            check(lib.b200ps_dense_apply_sgd(p, g, self.plan.W, n, self.lr, mir, len(L.mirror_ranks), self._stream()))
+        else:
+            m, v = self.state[L.shard]
+            o = 4 * (lo - L.begin)
+            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr() + o), C.c_void_p(v.data_ptr() + o), g,
+                                              self.plan.W, n, C.byref(a), mir, len(L.mirror_ranks), self._stream()))
+
+    def step(self):
+        """push + aggregate + apply + pull for every local shard; gradients are already in the
+        workers' device buffers (`grad_buffer`)."""
+        self.t += 1
+        a = self._opt_scalars()
+        if self.transport == "nccl" and self.world > 1:
+            return self._step_nccl(a)
+        self._barrier()  # every worker's gradient is in place
+        for L in self.plan.launches:
+            if L.end > L.begin:
+                self._launch(L, L.begin, L.end, a)
+        self._barrier()  # every replica holds every updated slice
+
+    def _step_nccl(self, a):
+        import torch.distributed as dist
+
+        L = self.plan.launches[0]
+        n = L.end - L.begin
+        g = self.grads[self.plan.local_workers[0]]
+        dist.reduce_scatter_tensor(self._gsum, g, op=dist.ReduceOp.AVG, group=self.group)
+        gp = _ptrs([self._gsum.data_ptr()])
+        p = C.c_void_p(self.arena.ptr + 4 * L.begin)
+        if a is None:
+            check(lib.b200ps_dense_apply_sgd(p, gp, 1, n, self.lr, _ptrs([]), 0, self._stream()))
+        else:
+            m, v = self.state[L.shard]
+            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr()), C.c_void_p(v.data_ptr()), gp, 1, n,
+                                              C.byref(a), _ptrs([]), 0, self._stream()))
+        dist.all_gather_into_tensor(self.replica, self.replica[L.begin:L.end], group=self.group)
+
+    # ---- worker-facing ------------------------------------------------------------------------
+    def grad_buffer(self, worker: int) -> torch.Tensor:
+        """Device buffer a local worker writes its gradient into (zero-copy push)."""
+        return self.grads[worker]
+
+    def push(self, worker: int, host_grad: torch.Tensor):
+        """H2D of one local worker's gradient (pinned host memory), asynchronous."""
+        self.grads[worker].copy_(host_grad, non_blocking=True)
+
+    def pull(self, worker: int, host_out: torch.Tensor):
+        """D2H of the replica into a local worker's host buffer, asynchronous."""
+        if worker not in self.grads:
+            raise KeyError(f"worker {worker} is not placed on rank {self.rank}")
+        host_out.copy_(self.replica, non_blocking=True)
+
+    def step_host(self, host_grads: Dict[int, torch.Tensor], host_out: Dict[int, torch.Tensor]):
+        """A whole step with HOST buffers: every local worker's gradient goes host -> device, the
+        step runs, and the updated parameters go device -> host into every local worker's buffer.
+        With one GPU the three phases are pipelined chunk by chunk over three streams."""
+        if self.world > 1:
+            for w, h in host_grads.items():
+                self.push(w, h)
+            self.step()
+            for w, h in host_out.items():
+                self.pull(w, h)
+            return
+        self.t += 1
+        a = self._opt_scalars()
+        cur = torch.cuda.current_stream()
+        self._s_in.wait_stream(cur)
+        for L in self.plan.launches:
+            for lo in range(L.begin, L.end, self.chunk):
+                hi = min(lo + self.chunk, L.end)
+                with torch.cuda.stream(self._s_in):
+                    for w, h in host_grads.items():
+                        self.grads[w][lo:hi].copy_(h[lo:hi], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(self._s_in)
+                cur.wait_event(ev)
+                self._launch(L, lo, hi, a)
+                ev2 = torch.cuda.Event()
+                ev2.record(cur)
+                self._s_out.wait_event(ev2)
+                with torch.cuda.stream(self._s_out):
+                    for w, h in host_out.items():
+                        h[lo:hi].copy_(self.replica[lo:hi], non_blocking=True)
+        cur.wait_stream(self._s_out)
+
+    # ---- inspection ---------------------------------------------------------------------------
+    def dump(self) -> Dict[int, Dict[str, np.ndarray]]:
+        """Local slices: {shard: {"range": (b, e), "p": ..., "m": ..., "v": ...}} as NumPy arrays."""
+        torch.cuda.synchronize()
+        out = {}
+        for L in self.plan.launches:
+            d = {"range": (L.begin, L.end), "p": self.replica[L.begin:L.end].cpu().numpy()}
+            if L.shard in self.state:
+                d["m"], d["v"] = (x.cpu().numpy() for x in self.state[L.shard])
+            out[L.shard] = d
+        return out
+
+    def algorithmic_bytes_per_step(self) -> int:
+        """(4W + 8) n for SGD, (4W + 24) n for Adam, summed over local slices."""
+        k = 4 * self.plan.W + (24 if self.optimizer == "adam" else 8)
+        return sum(k * (L.end - L.begin) for L in self.plan.launches)

@@ -1,0 +1,185 @@
+"""GPU parity of the dense PS step (a5..a9) against the oracle: BIT-EXACT (fixed worker order,
+one rounding per operation), through the C ABI (ctypes -> libb200ps.so)."""
+import ctypes
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+import b200ps
+from b200ps import kernels as K
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def bits(t):
+    return t.detach().cpu().numpy().view(np.uint32)
+
+
+def same(t, a):
+    return np.array_equal(bits(t), np.ascontiguousarray(a).view(np.uint32))
+
+
+def test_library_is_the_cuda_one():
+    assert torch.cuda.is_available()
+    assert b200ps.LIB_PATH.endswith("libb200ps.so")
+    assert torch.cuda.get_device_capability(0)[0] >= 10, "built for sm_100a only"
+
+
+@pytest.mark.parametrize("n,first", [(1, 0), (1000, 5), (1 << 20, 1 << 40), (4097, 123456789)])
+def test_fill_uniform_bit_exact(oracle, n, first):
+    d = torch.empty(n, dtype=torch.float32, device="cuda")
+    K.fill_uniform(d, seed=2, step=7, worker=3, first=first)
+    assert same(d, oracle.fill_uniform(n, 2, 7, 3, first=first, threads=4))
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4, 5, 8, 9, 16, 64])
+@pytest.mark.parametrize("n", [1, 3, 4, 1024, 4099, 262144 + 5])
+def test_sgd_bit_exact(oracle, W, n):
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    grads = [oracle.fill_uniform(n, 2, 1, w) for w in range(W)]
+    dp, dg = dev(p), [dev(g) for g in grads]
+    for step in range(3):
+        K.dense_apply_sgd(dp, dg, 0.05)
+        oracle.dense_sgd(p, grads, 0.05, threads=4)
+    assert same(dp, p)
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4, 7, 8, 12])
+@pytest.mark.parametrize("n", [1, 5, 2048, 4099, 300001])
+def test_adam_bit_exact_10_steps(oracle, W, n):
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    m, v = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    dp, dm, dv = dev(p), dev(m), dev(v)
+    dg = [torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(W)]
+    for t in range(1, 11):
+        grads = [oracle.fill_uniform(n, 2, t, w, threads=4) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(dg[w], 2, t, w)  # gradients produced on the device by the same hash
+        K.dense_apply_adam(dp, dm, dv, dg, K.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t))
+        oracle.dense_adam(p, m, v, grads, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), threads=4)
+    assert same(dp, p) and same(dm, m) and same(dv, v)
+    # the north-star tolerance (1e-6 relative) holds a fortiori
+    assert np.allclose(dp.cpu().numpy(), p, rtol=1e-6, atol=0)
+
+
+@pytest.mark.parametrize("threads,ctas,unroll", [(128, 8, 1), (256, 4, 2), (512, 2, 4), (1024, 1, 2), (256, 16, 4)])
+def test_every_launch_geometry_gives_the_same_bits(oracle, threads, ctas, unroll):
+    n, W = 1_000_003, 4
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    m, v = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    grads = [oracle.fill_uniform(n, 2, 1, w, threads=4) for w in range(W)]
+    dp, dm, dv, dg = dev(p), dev(m), dev(v), [dev(g) for g in grads]
+    K.set_dense_tuning(threads, ctas, unroll)
+    try:
+        K.dense_apply_adam(dp, dm, dv, dg, K.adam_scalars(1e-3, t=1))
+        ds = dev(p)
+        K.dense_apply_sgd(ds, dg, 0.1)
+    finally:
+        K.set_dense_tuning(256, 4, 2)
+    oracle.dense_adam(p, m, v, grads, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 1), threads=4)
+    assert same(dp, p) and same(dm, m) and same(dv, v)
+    assert same(ds, oracle.dense_sgd(oracle.fill_uniform(n, 1, 0, 0), grads, 0.1, threads=4))
+
+
+def test_unaligned_pointers_take_the_scalar_path(oracle):
+    n, W = 10_001, 3
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    grads = [oracle.fill_uniform(n, 2, 1, w) for w in range(W)]
+    base = torch.empty(n + 1, dtype=torch.float32, device="cuda")
+    dp = base[1:]  # 4-byte aligned only
+    dp.copy_(torch.from_numpy(p))
+    dg = [dev(g) for g in grads]
+    K.dense_apply_sgd(dp, dg, 0.25)
+    assert same(dp, oracle.dense_sgd(p, grads, 0.25))
+
+
+def test_mirrors_receive_the_updated_slice(oracle):
+    # pull fused into the step: the new parameters land in every worker copy
+    n, W = 50_000, 2
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    grads = [oracle.fill_uniform(n, 2, 1, w) for w in range(W)]
+    dp, dg = dev(p), [dev(g) for g in grads]
+    mirrors = [torch.zeros(n, dtype=torch.float32, device="cuda") for _ in range(3)]
+    m, v = torch.zeros_like(dp), torch.zeros_like(dp)
+    K.dense_apply_adam(dp, m, v, dg, K.adam_scalars(1e-3, t=1), mirrors=mirrors)
+    for mi in mirrors:
+        assert torch.equal(mi, dp)
+    oracle.dense_adam(p, np.zeros(n, np.float32), np.zeros(n, np.float32), grads, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 1))
+    assert same(dp, p)
+
+
+def test_sharded_application_equals_whole(oracle):
+    """Size-independent property: applying the step slice by slice (any shard count) gives the
+    bits of applying it to the whole buffer -- the PS shards are independent."""
+    sizes = b200ps.synth.resnet50_c3_variables()
+    W = 4
+    whole = b200ps.ShardMap(sizes, 1)
+    P = whole.total
+    p0 = torch.empty(P, dtype=torch.float32, device="cuda")
+    K.fill_uniform(p0, 1, 0, 0)
+    dg = [K.fill_uniform(torch.empty(P, dtype=torch.float32, device="cuda"), 2, 1, w) for w in range(W)]
+    ref = p0.clone()
+    rm, rv = torch.zeros_like(ref), torch.zeros_like(ref)
+    opt = K.adam_scalars(1e-3, t=1)
+    K.dense_apply_adam(ref, rm, rv, dg, opt)
+    for S in (2, 4, 8):
+        sm = b200ps.ShardMap(sizes, S)
+        p, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+        for b, e in sm.slices():
+            K.dense_apply_adam(p[b:e], m[b:e], v[b:e], [g[b:e] for g in dg], opt)
+        assert torch.equal(p, ref) and torch.equal(m, rm) and torch.equal(v, rv)
+    # and the whole thing against the oracle at C3's full size
+    hp = oracle.fill_uniform(P, 1, 0, 0, threads=8)
+    hg = [oracle.fill_uniform(P, 2, 1, w, threads=8) for w in range(W)]
+    hm, hv = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 1), threads=8)
+    assert same(ref, hp) and same(rm, hm) and same(rv, hv)
+
+
+def test_c1_full_size_two_shards_four_workers(oracle):
+    """BASELINE configs[1] at full size: 100 685 824 params, 2 PS shards, 4 workers, Adam, 2 steps."""
+    sm = b200ps.ShardMap(b200ps.synth.mlp_c1_variables(), 2)
+    P, W = sm.total, 4
+    nt = oracle.max_threads()
+    dp = K.fill_uniform(torch.empty(P, dtype=torch.float32, device="cuda"), 1, 0, 0)
+    dm, dv = torch.zeros_like(dp), torch.zeros_like(dp)
+    dg = [torch.empty(P, dtype=torch.float32, device="cuda") for _ in range(W)]
+    hp = oracle.fill_uniform(P, 1, 0, 0, threads=nt)
+    hm, hv = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    for t in (1, 2):
+        for w in range(W):
+            K.fill_uniform(dg[w], 2, t, w)
+        hg = [oracle.fill_uniform(P, 2, t, w, threads=nt) for w in range(W)]
+        opt = K.adam_scalars(1e-3, t=t)
+        for b, e in sm.slices():
+            K.dense_apply_adam(dp[b:e], dm[b:e], dv[b:e], [g[b:e] for g in dg], opt)
+        oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), threads=nt)
+    assert same(dp, hp) and same(dm, hm) and same(dv, hv)
+
+
+def test_argument_errors_are_statuses_not_crashes():
+    p = torch.zeros(8, dtype=torch.float32, device="cuda")
+    with pytest.raises(b200ps.B200PSError):
+        K.dense_apply_sgd(p, [], 0.1)  # W = 0
+    with pytest.raises(b200ps.B200PSError):
+        K.dense_apply_sgd(p, [p] * 65, 0.1)  # W > B200PS_MAX_WORKERS
+    with pytest.raises(b200ps.B200PSError):
+        K.dense_apply_sgd(p, [p], 0.1, mirrors=[p] * 9)
+    with pytest.raises(TypeError):
+        K.dense_apply_sgd(torch.zeros(8), [p], 0.1)  # CPU tensor: there is no fallback
+    K.dense_apply_sgd(p, [p], 0.1, n=0)  # empty slice is a no-op
+    torch.cuda.synchronize()
+
+
+def test_launch_counter_counts():
+    p = torch.zeros(1024, dtype=torch.float32, device="cuda")
+    before = K.launch_count()
+    K.dense_apply_sgd(p, [p], 0.1)
+    K.fill_uniform(p, 1, 1, 1)
+    assert K.launch_count() == before + 2
