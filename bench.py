@@ -74,7 +74,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, device_index: int):
         super().__init__(daemon=True)
-        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.samples, self.reasons, self.max_mhz, self._halt = [], set(), None, threading.Event()
         self.err = None
         try:
             import pynvml
@@ -95,7 +95,7 @@ class ClockSampler(threading.Thread):
     def run(self):
         if not self.nv:
             return
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
                 bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
@@ -108,7 +108,7 @@ class ClockSampler(threading.Thread):
             time.sleep(0.005)
 
     def finish(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=2)
         s = sorted(self.samples)
         out = {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),

@@ -214,20 +214,39 @@ __global__ void fill_uniform_kernel(float* __restrict__ dst, uint64_t n, uint64_
 }
 
 struct Tuning {
+    // measured on B200 (profiles/r1_dense_sweep.md): 256 x 8 x 2 streams Adam W=4 at 6.5 TB/s
     int threads = 256;
-    int ctas_per_sm = 4;
+    int ctas_per_sm = 8;
     int unroll = 2;
 };
 Tuning g_tuning;
 
+// largest CTA the kernel's register count allows (1024 threads x > 64 registers does not fit an SM)
+template <typename Kern>
+int max_threads_for(Kern kern) {
+    cudaFuncAttributes fa{};
+    return cudaFuncGetAttributes(&fa, kern) == cudaSuccess ? fa.maxThreadsPerBlock : 256;
+}
+
+template <int OPT, int WT, int U>
+cudaError_t launch_k(const DenseParams& a, int grid, int threads, cudaStream_t st) {
+    static const int limit = max_threads_for(dense_apply_kernel<OPT, WT, U>);
+    if (threads > limit) {  // keep the thread count of the launch constant: more, smaller CTAs
+        const int t2 = limit / 32 * 32;
+        grid = (int)(((long long)grid * threads + t2 - 1) / t2);
+        threads = t2;
+    }
+    dense_apply_kernel<OPT, WT, U><<<grid, threads, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
 template <int OPT, int WT>
 cudaError_t launch_u(const DenseParams& a, int grid, int threads, int unroll, cudaStream_t st) {
     switch (unroll) {
-        case 1: dense_apply_kernel<OPT, WT, 1><<<grid, threads, 0, st>>>(a); break;
-        case 4: dense_apply_kernel<OPT, WT, 4><<<grid, threads, 0, st>>>(a); break;
-        default: dense_apply_kernel<OPT, WT, 2><<<grid, threads, 0, st>>>(a); break;
+        case 1: return launch_k<OPT, WT, 1>(a, grid, threads, st);
+        case 4: return launch_k<OPT, WT, 4>(a, grid, threads, st);
+        default: return launch_k<OPT, WT, 2>(a, grid, threads, st);
     }
-    return cudaGetLastError();
 }
 
 template <int OPT>

@@ -81,7 +81,7 @@ def test_every_launch_geometry_gives_the_same_bits(oracle, threads, ctas, unroll
         ds = dev(p)
         K.dense_apply_sgd(ds, dg, 0.1)
     finally:
-        K.set_dense_tuning(256, 4, 2)
+        K.set_dense_tuning(256, 8, 2)
     oracle.dense_adam(p, m, v, grads, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 1), threads=4)
     assert same(dp, p) and same(dm, m) and same(dv, v)
     assert same(ds, oracle.dense_sgd(oracle.fill_uniform(n, 1, 0, 0), grads, 0.1, threads=4))
