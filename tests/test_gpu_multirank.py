@@ -1,0 +1,48 @@
+"""N > 1 on real GPUs: one process per GPU, gradients read from and parameters written to peer
+memory inside the step kernel.  Skipped on a 1-GPU box (run with `gpurun --gpus 2`)."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+torch = pytest.importorskip("torch")
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run(n, S, W, opt, transport):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", str(_port()), os.path.join(HERE, "_mr_worker.py"), str(S), str(W), opt, transport]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "MULTIRANK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("S,W,opt", [(2, 4, "adam"), (2, 2, "sgd"), (3, 5, "adam"), (1, 2, "adam")])
+def test_peer_fused_step_is_bit_exact_on_every_replica(S, W, opt):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, S, W, opt, "peer")
+
+
+def test_all_gpus_of_the_box():
+    n = torch.cuda.device_count()
+    if n < 4:
+        pytest.skip("needs >= 4 GPUs")
+    _run(n, 2 * n, 4 * n, "adam", "peer")
+
+
+def test_nccl_transport_matches_within_tolerance():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, 2, 2, "adam", "nccl")
