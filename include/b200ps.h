@@ -156,6 +156,56 @@ int b200ps_ipc_export(const void* d_ptr, void* handle_out /* B200PS_IPC_HANDLE_B
 int b200ps_ipc_open(const void* handle, void** d_ptr); /* maps a peer's allocation */
 int b200ps_ipc_close(void* d_ptr);
 
+/* ------------------------------------------------------------------------------------------------
+ * Sparse group: embedding tables sharded by rows (TF "div" partitioning), SURVEY.md 8(a) rows
+ * a10..a12.  Reference: none -- TensorFlow's embedding_lookup over a partitioned variable and its
+ * sparse optimizer ops on the PS tasks of k8s-operator.md:6.
+ *
+ * Shard s of the table lives on GPU s mod world.  d_shard_base[s] is row 0 of shard s; d_ids[w] /
+ * d_grad_rows[w] are worker w's ids (int64) and gradient rows ([ids_per_worker, dim] fp32).  Any
+ * of these may be peer-mapped pointers: the kernels read ids and rows where they live, so the
+ * routing all-to-all is fused into them.
+ *
+ *   pull  out[k, :] = table[ids[k], :]                      (an out-of-range id gives a zero row)
+ *   push  1. sort_segment: the entries (id, worker, position) of THIS GPU's shards, stably sorted
+ *            by id -> sorted ids, source permutation, segment ids, unique ids, segment offsets
+ *            (all in the workspace; counts stay on the device)
+ *         2. apply: per unique id, G = (1/W) * fold of its gradient rows in sorted order (left
+ *            fold; segments over 256 entries chunk-wise, see oracle/ps_oracle.c), then
+ *            SGD     row -= lr * G
+ *            Adagrad a += G*G; row -= (lr * G) / sqrt(a)       -- only touched rows change
+ * Integer results are bit-exact against the oracle, and so are the rows (fixed fold order).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    uint64_t rows; /* rows of the whole table, < 2^32 */
+    int dim;       /* floats per row: multiple of 4, 4..4096 */
+    int nshards;   /* S, <= B200PS_MAX_WORKERS */
+    int rank;      /* this GPU hosts the shards s with s % world == rank */
+    int world;
+} b200ps_table_geom_t;
+
+int b200ps_sparse_gather(float* d_out, const float* const* d_shard_base, const b200ps_table_geom_t* geom,
+                         const int64_t* d_ids, uint64_t n, void* stream);
+/* scratch for one push of n_total = W * ids_per_worker entries (256-byte aligned device memory
+ * the caller owns; contents are the plan the apply call reads) */
+size_t b200ps_sparse_workspace_bytes(uint64_t n_total);
+int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, uint64_t ids_per_worker,
+                               const b200ps_table_geom_t* geom, void* d_workspace, size_t workspace_bytes,
+                               void* stream);
+int b200ps_sparse_apply_sgd(float* const* d_shard_base, const float* const* d_grad_rows, int W,
+                            uint64_t ids_per_worker, const b200ps_table_geom_t* geom, float lr,
+                            const void* d_workspace, void* stream);
+int b200ps_sparse_apply_adagrad(float* const* d_shard_base, float* const* d_accum_base,
+                                const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
+                                const b200ps_table_geom_t* geom, float lr, const void* d_workspace,
+                                void* stream);
+/* Debug accessor for the bit-exact checks: copies the plan of the last sort_segment to the host
+ * (synchronises the stream).  Arrays may be NULL; sizes: n_kept for sorted ids / perm / segment
+ * ids, n_unique for unique ids, n_unique + 1 for segment offsets (allocate n_total [+1]). */
+int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t rows, uint64_t* n_kept,
+                            uint64_t* n_unique, uint64_t* n_bad, int64_t* h_sorted_ids, uint32_t* h_perm,
+                            int32_t* h_seg_id, int64_t* h_unique_ids, uint32_t* h_seg_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

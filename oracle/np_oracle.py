@@ -103,16 +103,24 @@ def sort_segment(ids):
     return s, perm, seg_id, s[head], np.concatenate((starts, [np.uint32(len(s))])).astype(np.uint32)
 
 
+SEG_CHUNK = 256
+
+
 def segment_mean_rows(grad_rows, perm, seg_offset, inv_w):
-    """Left fold of the rows of each segment in sorted order, then one multiply by inv_w."""
+    """Fixed-order fold of the rows of each segment in sorted order, then one multiply by inv_w.
+    Up to SEG_CHUNK entries: a plain left fold.  Longer: each chunk of SEG_CHUNK consecutive
+    entries left to right, then the chunk sums left to right."""
     nu = len(seg_offset) - 1
     out = np.empty((nu, grad_rows.shape[1]), np.float32)
     for u in range(nu):
         a, b = int(seg_offset[u]), int(seg_offset[u + 1])
-        acc = grad_rows[perm[a]].astype(np.float32, copy=True)
-        for j in range(a + 1, b):
-            acc = acc + grad_rows[perm[j]]
-        out[u] = acc * np.float32(inv_w)
+        total = None
+        for c0 in range(a, b, SEG_CHUNK):
+            acc = grad_rows[perm[c0]].astype(np.float32, copy=True)
+            for j in range(c0 + 1, min(c0 + SEG_CHUNK, b)):
+                acc = acc + grad_rows[perm[j]]
+            total = acc if total is None else total + acc
+        out[u] = total * np.float32(inv_w)
     return out
 
 

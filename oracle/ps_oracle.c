@@ -214,6 +214,22 @@ uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, ui
 
 /* ---------------------------------------------------------------- a12: segmented apply */
 
+/* Fixed-order segment sum of one column.  Segments of at most PS_SEG_CHUNK entries are a plain left
+ * fold in sorted order; longer ones (hot ids under Zipf skew) are folded chunk by chunk -- each chunk
+ * of PS_SEG_CHUNK consecutive entries left to right, then the chunk sums left to right -- so that a
+ * GPU can give the chunks of one hot row to different warps and still produce these bits. */
+static float segment_sum(const float* grad_rows, const uint32_t* perm, uint32_t a, uint32_t b, int dim, int d) {
+    float total = 0.0f;
+    uint32_t c0, j;
+    for (c0 = a; c0 < b; c0 += PS_SEG_CHUNK) {
+        uint32_t c1 = b - c0 < PS_SEG_CHUNK ? b : c0 + PS_SEG_CHUNK;
+        float acc = grad_rows[(uint64_t)perm[c0] * (uint64_t)dim + (uint64_t)d];
+        for (j = c0 + 1; j < c1; ++j) acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
+        total = (c0 == a) ? acc : total + acc;
+    }
+    return total;
+}
+
 void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* grad_rows,
                          const uint32_t* perm, const int64_t* unique_ids,
                          const uint32_t* seg_offset, uint64_t n_unique, float inv_w, float lr) {
@@ -222,11 +238,7 @@ void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* g
     for (u = 0; u < n_unique; ++u) {
         float* row = table + (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
         for (d = 0; d < dim; ++d) {
-            uint32_t j = seg_offset[u];
-            float acc = grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d], g;
-            for (++j; j < seg_offset[u + 1]; ++j)
-                acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
-            g = acc * inv_w;
+            float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w;
             row[d] = row[d] - lr * g;
         }
     }
@@ -241,11 +253,7 @@ void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_ba
     for (u = 0; u < n_unique; ++u) {
         uint64_t base = (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
         for (d = 0; d < dim; ++d) {
-            uint32_t j = seg_offset[u];
-            float acc = grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d], g, an;
-            for (++j; j < seg_offset[u + 1]; ++j)
-                acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
-            g = acc * inv_w;
+            float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w, an;
             an = accum[base + d] + g * g;
             accum[base + d] = an;
             table[base + d] = table[base + d] - (lr * g) / sqrtf(an);

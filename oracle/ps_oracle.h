@@ -72,7 +72,8 @@ uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, ui
                          int32_t* seg_id, int64_t* unique_ids, uint32_t* seg_offset);
 
 /* ---- a12: segmented scatter-add + apply ---- */
-/* G_u = inv_w * left-fold of grad rows in sorted order; SGD: row -= lr*G_u */
+#define PS_SEG_CHUNK 256u /* segments longer than this are folded chunk-wise (see ps_oracle.c) */
+/* G_u = inv_w * fixed-order fold of grad rows in sorted order; SGD: row -= lr*G_u */
 void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* grad_rows,
                          const uint32_t* perm, const int64_t* unique_ids,
                          const uint32_t* seg_offset, uint64_t n_unique, float inv_w, float lr);

@@ -20,6 +20,10 @@ class B200PSError(RuntimeError):
         self.status = status
 
 
+class TableGeom(C.Structure):
+    _fields_ = [("rows", C.c_uint64), ("dim", C.c_int), ("nshards", C.c_int), ("rank", C.c_int), ("world", C.c_int)]
+
+
 class AdamScalars(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("lr_t", "beta1", "beta2", "omb1", "omb2", "eps")]
 
@@ -37,6 +41,7 @@ _u64, _i32, _u32, _f32, _vp, _cp, _sz = C.c_uint64, C.c_int, C.c_uint32, C.c_flo
 _pp = C.POINTER(C.c_void_p)
 
 # name -> (restype, argtypes); mirrors include/b200ps.h one to one (tests/test_abi.py checks it)
+# (TableGeom / AdamScalars mirror the structs of the header)
 SIGNATURES = {
     "b200ps_last_error": (_cp, []),
     "b200ps_version": (_i32, []),
@@ -70,6 +75,13 @@ SIGNATURES = {
     "b200ps_ipc_export": (_i32, [_vp, _vp]),
     "b200ps_ipc_open": (_i32, [_vp, _pp]),
     "b200ps_ipc_close": (_i32, [_vp]),
+    "b200ps_sparse_gather": (_i32, [_vp, _vp, C.POINTER(TableGeom), _vp, _u64, _vp]),
+    "b200ps_sparse_workspace_bytes": (_sz, [_u64]),
+    "b200ps_sparse_sort_segment": (_i32, [_vp, _i32, _u64, C.POINTER(TableGeom), _vp, _sz, _vp]),
+    "b200ps_sparse_apply_sgd": (_i32, [_vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp, _vp]),
+    "b200ps_sparse_apply_adagrad": (_i32, [_vp, _vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp, _vp]),
+    "b200ps_sparse_plan_read": (_i32, [_vp, _u64, _u64, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64), _vp, _vp, _vp,
+                                        _vp, _vp, _vp]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -1,0 +1,671 @@
+// sparse.cu -- embedding tables on the PS: gather (pull) and deterministic sorted-segment
+// scatter-add + apply (push), include/b200ps.h "Sparse group"; SURVEY.md 8(a) rows a10..a12.
+//
+// Reference: none -- the reference states only the PS / WORKER roles (k8s-operator.md:6); in a
+// TFJob this is TensorFlow's embedding_lookup over a partitioned variable and its sparse
+// optimizer ops on the PS tasks.
+//
+// Rows are partitioned over S shards by TF "div" (the first rows % S shards hold one row more);
+// shard s lives on GPU s mod G.  Everything is addressed through per-shard / per-worker base
+// pointers that may be peer-mapped (ipc.cu), so routing is not a separate exchange step: the
+// kernels of one GPU read all workers' ids and gradient rows wherever they live.
+//
+// push on one GPU, all device-side (no host round trip; counts stay in the workspace header):
+//   1. stable partition of the W*B (worker, position)-ordered ids: keep those of this GPU's shards
+//   2. stable LSD radix sort of the kept ids, 8 bits per pass, ceil(log2(rows)/8) passes,
+//      payload = source entry index -> order (id, worker, position)
+//   3. heads + scan -> segment ids, unique ids, segment offsets
+//   4. one lane group per unique id folds its gradient rows in that fixed order (chunks of 256,
+//      see oracle/ps_oracle.c segment_sum), scales by 1/W and updates the row (SGD / Adagrad)
+// Integer outputs are bit-exact against the oracle; the fold order makes the rows bit-exact too.
+//
+// HBM-bound integer/byte work: ids 8 B, rows dim*4 B; sort passes are overhead traffic
+// (12 B per kept id per pass).  No tensor cores.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <vector>
+
+#include "common.h"
+#include "cuda_util.h"
+
+namespace b200ps {
+namespace {
+
+constexpr int TILE_THREADS = 256;
+constexpr int ITEMS = 8;
+constexpr int TILE = TILE_THREADS * ITEMS;  // entries per CTA in the partition / radix passes
+constexpr int WARPS = TILE_THREADS / 32;
+constexpr int BINS = 256;
+constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_TILE = SCAN_THREADS * 4;
+constexpr uint32_t SEG_CHUNK = 256;  // == PS_SEG_CHUNK of the oracle
+constexpr uint32_t NONE = 0xFFFFFFFFu;
+
+enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_FINAL = 3, HDR_WORDS = 64 };
+
+struct Geom {
+    uint64_t rows;
+    uint64_t q, r, t;  // div partition: q = rows / S, r = rows % S, t = r * (q + 1)
+    int dim, nshards, rank, world;
+};
+
+struct IdSources {
+    const int64_t* ids[B200PS_MAX_WORKERS];
+    uint32_t per_worker;
+    uint32_t n_total;
+};
+
+struct RowSources {
+    const float* rows[B200PS_MAX_WORKERS];
+    uint32_t per_worker;
+};
+
+struct ShardBases {
+    float* base[B200PS_MAX_WORKERS];   // row 0 of shard s (table)
+    float* accum[B200PS_MAX_WORKERS];  // row 0 of shard s (Adagrad accumulator) or null
+};
+
+__device__ __forceinline__ int owner_of(const Geom& g, uint64_t id, uint64_t* local_row) {
+    if (id < g.t) {
+        const uint64_t s = id / (g.q + 1);
+        *local_row = id - s * (g.q + 1);
+        return (int)s;
+    }
+    const uint64_t k = (id - g.t) / g.q;
+    *local_row = (id - g.t) - k * g.q;
+    return (int)(g.r + k);
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace
+// ------------------------------------------------------------------------------------------------
+struct Workspace {
+    uint32_t* hdr;
+    uint32_t* key[2];
+    uint32_t* val[2];
+    uint32_t* hist;       // BINS * nb
+    uint32_t* scan_sums;  // block sums of the generic scan
+    uint32_t* seg;        // n + 1: head-count scan, then segment ids
+    uint32_t* unique;     // n
+    uint32_t* seg_off;    // n + 1
+    uint32_t nb;
+    size_t bytes;
+};
+
+size_t align_up(size_t x) { return (x + 255) / 256 * 256; }
+
+Workspace carve(void* base, uint64_t n) {
+    Workspace w{};
+    char* p = (char*)base;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        void* r = p ? (void*)(p + off) : nullptr;
+        off += align_up(bytes);
+        return r;
+    };
+    w.nb = (uint32_t)((n + TILE - 1) / TILE);
+    if (w.nb == 0) w.nb = 1;
+    w.hdr = (uint32_t*)take(HDR_WORDS * 4);
+    for (int i = 0; i < 2; ++i) w.key[i] = (uint32_t*)take(n * 4);
+    for (int i = 0; i < 2; ++i) w.val[i] = (uint32_t*)take(n * 4);
+    w.hist = (uint32_t*)take((size_t)BINS * w.nb * 4);
+    const size_t longest = (size_t)BINS * w.nb > n + 1 ? (size_t)BINS * w.nb : n + 1;
+    w.scan_sums = (uint32_t*)take(((longest + SCAN_TILE - 1) / SCAN_TILE + 1) * 4);
+    w.seg = (uint32_t*)take((n + 1) * 4);
+    w.unique = (uint32_t*)take(n * 4);
+    w.seg_off = (uint32_t*)take((n + 1) * 4);
+    w.bytes = off;
+    return w;
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic exclusive scan of uint32 (three launches; in place allowed)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* total) {
+    __shared__ uint32_t warp_sums[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    uint32_t inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += y;
+    }
+    __syncthreads();  // protects warp_sums across repeated calls
+    if (lane == 31) warp_sums[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t s = lane < nw ? warp_sums[lane] : 0, si = s;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, si, d);
+            if (lane >= d) si += y;
+        }
+        warp_sums[lane] = si - s;  // exclusive warp offsets
+        if (lane == 31) warp_sums[31] = si - s, *total = si;
+    }
+    __syncthreads();
+    return inc - x + warp_sums[wid];
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(const uint32_t* __restrict__ in, uint32_t n,
+                                                                   uint32_t* __restrict__ sums) {
+    __shared__ uint32_t total;
+    const uint32_t i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (i0 + k < n) s += in[i0 + k];
+    block_exclusive_scan(s, &total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_sums_kernel(uint32_t* sums, uint32_t nblk) {
+    __shared__ uint32_t total;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < nblk; base += SCAN_THREADS) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t x = i < nblk ? sums[i] : 0;
+        const uint32_t e = block_exclusive_scan(x, &total);
+        if (i < nblk) sums[i] = carry + e;
+        carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sums[nblk] = carry;  // grand total
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_down_kernel(const uint32_t* in, uint32_t* out, uint32_t n,
+                                                                 const uint32_t* __restrict__ sums) {
+    __shared__ uint32_t total;
+    const uint32_t i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    uint32_t x[4], s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        x[k] = i0 + k < n ? in[i0 + k] : 0;
+        s += x[k];
+    }
+    uint32_t e = block_exclusive_scan(s, &total) + sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (i0 + k < n) out[i0 + k] = e;
+        e += x[k];
+    }
+}
+
+cudaError_t scan_exclusive(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* sums, cudaStream_t st, int* launches) {
+    const uint32_t nblk = (n + SCAN_TILE - 1) / SCAN_TILE;
+    scan_reduce_kernel<<<nblk, SCAN_THREADS, 0, st>>>(in, n, sums);
+    scan_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(sums, nblk);
+    scan_down_kernel<<<nblk, SCAN_THREADS, 0, st>>>(in, out, n, sums);
+    *launches += 3;
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// stable partition (MODE 0) and stable radix pass (MODE 1)
+// ------------------------------------------------------------------------------------------------
+struct PassArgs {
+    const uint32_t* key_in;
+    const uint32_t* val_in;
+    uint32_t* key_out;
+    uint32_t* val_out;
+    uint32_t* hist;  // BINS x nb, bin-major
+    uint32_t* hdr;
+    uint32_t nb;
+    int shift;
+};
+
+// One entry of the tile.  MODE 0 reads the workers' int64 ids and classifies keep (bin 0) / drop
+// (bin 1); MODE 1 reads the previous pass and takes 8 key bits.  Returns the bin or NONE.
+template <int MODE>
+__device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSources& src, const Geom& g, uint32_t idx,
+                                               uint32_t limit, uint32_t* key, uint32_t* val, bool count_bad) {
+    if (idx >= limit) return NONE;
+    if (MODE == 0) {
+        const uint32_t w = idx / src.per_worker, pos = idx - w * src.per_worker;
+        const int64_t id = src.ids[w][pos];
+        *val = idx;
+        if (id < 0 || (uint64_t)id >= g.rows) {
+            if (count_bad) atomicAdd(&a.hdr[HDR_BAD], 1u);
+            return 1;
+        }
+        *key = (uint32_t)id;
+        uint64_t lr;
+        return (owner_of(g, (uint64_t)id, &lr) % g.world) == g.rank ? 0u : 1u;
+    }
+    *key = a.key_in[idx];
+    *val = a.val_in[idx];
+    return (*key >> a.shift) & 255u;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(TILE_THREADS) pass_hist_kernel(const __grid_constant__ PassArgs a,
+                                                                 const __grid_constant__ IdSources src,
+                                                                 const __grid_constant__ Geom g) {
+    __shared__ uint32_t cnt[BINS];
+    cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t limit = MODE == 0 ? src.n_total : a.hdr[HDR_KEPT];
+    const uint32_t base = blockIdx.x * TILE;
+#pragma unroll
+    for (int b = 0; b < ITEMS; ++b) {
+        uint32_t key, val;
+        const uint32_t d = load_entry<MODE>(a, src, g, base + b * TILE_THREADS + threadIdx.x, limit, &key, &val, true);
+        if (d != NONE) atomicAdd(&cnt[d], 1u);
+    }
+    __syncthreads();
+    a.hist[threadIdx.x * a.nb + blockIdx.x] = cnt[threadIdx.x];
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid_constant__ PassArgs a,
+                                                                    const __grid_constant__ IdSources src,
+                                                                    const __grid_constant__ Geom g) {
+    __shared__ uint32_t cnt[WARPS][BINS];
+    for (int i = threadIdx.x; i < WARPS * BINS; i += TILE_THREADS) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t limit = MODE == 0 ? src.n_total : a.hdr[HDR_KEPT];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    // warp w owns entries [w*256, w*256+256) of the tile, 32 consecutive entries per batch: the
+    // (batch, lane) order is the input order, which makes the ranks stable
+    const uint32_t base = blockIdx.x * TILE + w * (32 * ITEMS);
+    uint32_t key[ITEMS], val[ITEMS], bin[ITEMS], rank[ITEMS];
+#pragma unroll
+    for (int b = 0; b < ITEMS; ++b) {
+        bin[b] = load_entry<MODE>(a, src, g, base + b * 32 + lane, limit, &key[b], &val[b], false);
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin[b]);
+        uint32_t start = 0;
+        if (bin[b] != NONE) start = cnt[w][bin[b]];
+        __syncwarp();
+        if (bin[b] != NONE && (peers & lt) == 0) cnt[w][bin[b]] = start + __popc(peers);
+        __syncwarp();
+        rank[b] = start + __popc(peers & lt);
+    }
+    __syncthreads();
+    {  // bin t: exclusive offsets over the warps, plus the global base of (bin, this CTA)
+        const int t = threadIdx.x;
+        uint32_t run = a.hist[t * a.nb + blockIdx.x];
+#pragma unroll
+        for (int k = 0; k < WARPS; ++k) {
+            const uint32_t c = cnt[k][t];
+            cnt[k][t] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int b = 0; b < ITEMS; ++b) {
+        if (bin[b] == NONE || (MODE == 0 && bin[b] != 0)) continue;
+        const uint32_t dst = cnt[w][bin[b]] + rank[b];
+        a.key_out[dst] = key[b];
+        a.val_out[dst] = val[b];
+    }
+    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = a.hist[1 * a.nb + 0];  // base of bin 1 = #kept
+}
+
+// ------------------------------------------------------------------------------------------------
+// segments
+// ------------------------------------------------------------------------------------------------
+__global__ void heads_kernel(const uint32_t* __restrict__ key, const uint32_t* __restrict__ hdr, uint32_t* __restrict__ flags,
+                             uint32_t n_plus_1) {
+    const uint32_t kept = hdr[HDR_KEPT];
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n_plus_1; k += gridDim.x * blockDim.x)
+        flags[k] = (k < kept && (k == 0 || key[k] != key[k - 1])) ? 1u : 0u;
+}
+
+// seg holds the exclusive head count e[k]; turn it into segment ids and emit unique ids / offsets
+__global__ void segments_kernel(const uint32_t* __restrict__ key, uint32_t* hdr, uint32_t* seg, uint32_t* __restrict__ unique,
+                                uint32_t* __restrict__ seg_off, uint32_t n) {
+    const uint32_t kept = hdr[HDR_KEPT];
+    const uint32_t n_unique = seg[n];  // flags beyond `kept` are 0, so e[n] is the head total
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < kept; k += gridDim.x * blockDim.x) {
+        const bool head = k == 0 || key[k] != key[k - 1];
+        const uint32_t sid = seg[k] + (head ? 1u : 0u) - 1u;
+        seg[k] = sid;
+        if (head) {
+            unique[sid] = key[k];
+            seg_off[sid] = k;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        hdr[HDR_UNIQUE] = n_unique;
+        seg_off[n_unique] = kept;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a12: one lane group per unique id
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_row4(const float* row, int c) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(reinterpret_cast<const float4*>(row) + c));
+    return r;
+}
+
+__device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
+    return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
+}
+
+__device__ __forceinline__ const float* grad_row(const RowSources& gs, uint32_t entry, int dim) {
+    const uint32_t w = entry / gs.per_worker, pos = entry - w * gs.per_worker;
+    return gs.rows[w] + (uint64_t)pos * (uint64_t)dim;
+}
+
+template <bool ADAGRAD>
+__device__ __forceinline__ float upd1(float g_sum, float row, float& acc, float inv_w, float lr) {
+    const float g = __fmul_rn(g_sum, inv_w);
+    if (!ADAGRAD) return __fsub_rn(row, __fmul_rn(lr, g));
+    acc = __fadd_rn(acc, __fmul_rn(g, g));
+    return __fsub_rn(row, __fdiv_rn(__fmul_rn(lr, g), __fsqrt_rn(acc)));
+}
+
+template <int LG, bool ADAGRAD>
+__global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant__ ShardBases tb,
+                                                           const __grid_constant__ RowSources gs,
+                                                           const __grid_constant__ Geom g, const uint32_t* __restrict__ hdr,
+                                                           const uint32_t* __restrict__ perm,
+                                                           const uint32_t* __restrict__ unique,
+                                                           const uint32_t* __restrict__ seg_off, float inv_w, float lr) {
+    const uint32_t n_unique = hdr[HDR_UNIQUE];
+    const int lane = threadIdx.x % LG;
+    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint32_t u = group; u < n_unique; u += ngroups) {
+        uint64_t lrow;
+        const int s = owner_of(g, unique[u], &lrow);
+        float* row = tb.base[s] + lrow * (uint64_t)g.dim;
+        float* arow = ADAGRAD ? tb.accum[s] + lrow * (uint64_t)g.dim : nullptr;
+        const uint32_t a = seg_off[u], b = seg_off[u + 1];
+        for (int c = lane; c < dim4; c += LG) {
+            float4 total = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (uint32_t c0 = a; c0 < b; c0 += SEG_CHUNK) {
+                const uint32_t c1 = b - c0 < SEG_CHUNK ? b : c0 + SEG_CHUNK;
+                float4 acc = ldg_row4(grad_row(gs, perm[c0], g.dim), c);
+                uint32_t j = c0 + 1;
+                for (; j + 4 <= c1; j += 4) {  // four rows in flight, added in order
+                    const float4 r0 = ldg_row4(grad_row(gs, perm[j], g.dim), c);
+                    const float4 r1 = ldg_row4(grad_row(gs, perm[j + 1], g.dim), c);
+                    const float4 r2 = ldg_row4(grad_row(gs, perm[j + 2], g.dim), c);
+                    const float4 r3 = ldg_row4(grad_row(gs, perm[j + 3], g.dim), c);
+                    acc = add4(add4(add4(add4(acc, r0), r1), r2), r3);
+                }
+                for (; j < c1; ++j) acc = add4(acc, ldg_row4(grad_row(gs, perm[j], g.dim), c));
+                total = c0 == a ? acc : add4(total, acc);
+            }
+            float4 r = reinterpret_cast<float4*>(row)[c];
+            float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ADAGRAD) ac = reinterpret_cast<float4*>(arow)[c];
+            r.x = upd1<ADAGRAD>(total.x, r.x, ac.x, inv_w, lr);
+            r.y = upd1<ADAGRAD>(total.y, r.y, ac.y, inv_w, lr);
+            r.z = upd1<ADAGRAD>(total.z, r.z, ac.z, inv_w, lr);
+            r.w = upd1<ADAGRAD>(total.w, r.w, ac.w, inv_w, lr);
+            reinterpret_cast<float4*>(row)[c] = r;
+            if (ADAGRAD) reinterpret_cast<float4*>(arow)[c] = ac;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a10: gather
+// ------------------------------------------------------------------------------------------------
+template <int LG>
+__global__ void __launch_bounds__(256) sparse_gather_kernel(float* __restrict__ out, const __grid_constant__ ShardBases tb,
+                                                            const __grid_constant__ Geom g, const int64_t* __restrict__ ids,
+                                                            uint64_t n) {
+    const int lane = threadIdx.x % LG;
+    const uint64_t group = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = (uint64_t)gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint64_t k = group; k < n; k += ngroups) {
+        const int64_t id = ids[k];
+        float4* dst = reinterpret_cast<float4*>(out + k * (uint64_t)g.dim);
+        if (id < 0 || (uint64_t)id >= g.rows) {  // out-of-range id: a row of zeros
+            for (int c = lane; c < dim4; c += LG) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            continue;
+        }
+        uint64_t lrow;
+        const int s = owner_of(g, (uint64_t)id, &lrow);
+        const float4* src = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
+        for (int c = lane; c < dim4; c += LG) dst[c] = src[c];
+    }
+}
+
+int lane_group(int dim) {
+    const int d4 = dim / 4;
+    int lg = 4;
+    while (lg < d4 && lg < 32) lg <<= 1;
+    return lg;
+}
+
+int make_geom(const b200ps_table_geom_t* in, Geom* g) {
+    B200PS_REQUIRE(in, B200PS_ERR_INVALID, "null table geometry");
+    B200PS_REQUIRE(in->rows >= 1 && in->rows <= 0xFFFFFFFFull, B200PS_ERR_RANGE, "rows must be in 1..2^32-1");
+    B200PS_REQUIRE(in->dim >= 4 && in->dim % 4 == 0 && in->dim <= 4096, B200PS_ERR_RANGE,
+                   "dim must be a multiple of 4 in 4..4096");
+    B200PS_REQUIRE(in->nshards >= 1 && in->nshards <= B200PS_MAX_WORKERS, B200PS_ERR_RANGE, "nshards must be in 1..%d",
+                   B200PS_MAX_WORKERS);
+    B200PS_REQUIRE(in->world >= 1 && in->rank >= 0 && in->rank < in->world, B200PS_ERR_RANGE, "rank %d of world %d", in->rank,
+                   in->world);
+    g->rows = in->rows;
+    g->q = in->rows / (uint64_t)in->nshards;
+    g->r = in->rows % (uint64_t)in->nshards;
+    g->t = g->r * (g->q + 1);
+    g->dim = in->dim;
+    g->nshards = in->nshards;
+    g->rank = in->rank;
+    g->world = in->world;
+    return B200PS_OK;
+}
+
+int key_passes(uint64_t rows) {
+    int bits = 1;
+    while (bits < 32 && (1ull << bits) < rows) ++bits;
+    return (bits + 7) / 8;
+}
+
+int fill_bases(const b200ps_table_geom_t* geom, float* const* table, float* const* accum, ShardBases* tb) {
+    B200PS_REQUIRE(table, B200PS_ERR_INVALID, "null shard base list");
+    memset(tb, 0, sizeof *tb);
+    for (int s = 0; s < geom->nshards; ++s) {
+        tb->base[s] = table[s];
+        tb->accum[s] = accum ? accum[s] : nullptr;
+        if (s % geom->world == geom->rank) {
+            B200PS_REQUIRE(table[s] && ((uintptr_t)table[s] & 15) == 0, B200PS_ERR_INVALID,
+                           "table shard %d must be a 16-byte aligned device pointer", s);
+            if (accum) B200PS_REQUIRE(accum[s] && ((uintptr_t)accum[s] & 15) == 0, B200PS_ERR_INVALID,
+                                      "accumulator shard %d must be a 16-byte aligned device pointer", s);
+        }
+    }
+    return B200PS_OK;
+}
+
+template <bool ADAGRAD>
+int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const float* const* d_grad_rows, int W,
+                 uint64_t ids_per_worker, const b200ps_table_geom_t* geom, float lr, const void* d_workspace, void* stream) {
+    Geom g;
+    if (int rc = make_geom(geom, &g)) return rc;
+    B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS && d_grad_rows && d_workspace, B200PS_ERR_INVALID,
+                   "bad worker count or null argument");
+    const uint64_t n = (uint64_t)W * ids_per_worker;
+    B200PS_REQUIRE(n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be below 2^32");
+    if (n == 0) return B200PS_OK;
+    ShardBases tb;
+    if (int rc = fill_bases(geom, d_shard_base, d_accum_base, &tb)) return rc;
+    RowSources gs{};
+    gs.per_worker = (uint32_t)ids_per_worker;
+    for (int w = 0; w < W; ++w) {
+        B200PS_REQUIRE(d_grad_rows[w] && ((uintptr_t)d_grad_rows[w] & 15) == 0, B200PS_ERR_INVALID,
+                       "gradient rows of worker %d must be a 16-byte aligned device pointer", w);
+        gs.rows[w] = d_grad_rows[w];
+    }
+    const Workspace ws = carve(const_cast<void*>(d_workspace), n);
+    const int passes = key_passes(g.rows);
+    const uint32_t* perm = ws.val[passes & 1];  // the partition wrote buffer 0, each radix pass flips
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const int lg = lane_group(g.dim);
+    const float inv_w = 1.0f / (float)W;
+    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
+    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_APPLY(LG) \
+    sparse_apply_kernel<LG, ADAGRAD><<<grid, 256, 0, st>>>(tb, gs, g, ws.hdr, perm, ws.unique, ws.seg_off, inv_w, lr)
+    switch (lg) {
+        case 4: LAUNCH_APPLY(4); break;
+        case 8: LAUNCH_APPLY(8); break;
+        case 16: LAUNCH_APPLY(16); break;
+        default: LAUNCH_APPLY(32); break;
+    }
+#undef LAUNCH_APPLY
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+}  // namespace
+}  // namespace b200ps
+
+using namespace b200ps;
+
+extern "C" size_t b200ps_sparse_workspace_bytes(uint64_t n_total) { return carve(nullptr, n_total ? n_total : 1).bytes; }
+
+extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_base, const b200ps_table_geom_t* geom,
+                                    const int64_t* d_ids, uint64_t n, void* stream) {
+    Geom g;
+    if (int rc = make_geom(geom, &g)) return rc;
+    B200PS_REQUIRE((d_out && d_ids) || n == 0, B200PS_ERR_INVALID, "null output or id pointer");
+    B200PS_REQUIRE(d_shard_base, B200PS_ERR_INVALID, "null shard base list");
+    if (n == 0) return B200PS_OK;
+    B200PS_REQUIRE(((uintptr_t)d_out & 15) == 0, B200PS_ERR_INVALID, "output must be 16-byte aligned");
+    ShardBases tb{};
+    for (int s = 0; s < g.nshards; ++s) {
+        B200PS_REQUIRE(d_shard_base[s] && ((uintptr_t)d_shard_base[s] & 15) == 0, B200PS_ERR_INVALID,
+                       "table shard %d must be a 16-byte aligned device pointer", s);
+        tb.base[s] = const_cast<float*>(d_shard_base[s]);
+    }
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const int lg = lane_group(g.dim);
+    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
+    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (lg) {
+        case 4: sparse_gather_kernel<4><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
+        case 8: sparse_gather_kernel<8><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
+        case 16: sparse_gather_kernel<16><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
+        default: sparse_gather_kernel<32><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
+    }
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, uint64_t ids_per_worker,
+                                          const b200ps_table_geom_t* geom, void* d_workspace, size_t workspace_bytes,
+                                          void* stream) {
+    Geom g;
+    if (int rc = make_geom(geom, &g)) return rc;
+    B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS && d_ids && d_workspace, B200PS_ERR_INVALID,
+                   "bad worker count or null argument");
+    const uint64_t n = (uint64_t)W * ids_per_worker;
+    B200PS_REQUIRE(n >= 1 && n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be in 1..2^32-2");
+    B200PS_REQUIRE(((uintptr_t)d_workspace & 255) == 0, B200PS_ERR_INVALID, "workspace must be 256-byte aligned");
+    const Workspace ws = carve(d_workspace, n);
+    B200PS_REQUIRE(workspace_bytes >= ws.bytes, B200PS_ERR_RANGE, "workspace of %zu bytes is too small: %zu needed",
+                   workspace_bytes, ws.bytes);
+    IdSources src{};
+    src.per_worker = (uint32_t)ids_per_worker;
+    src.n_total = (uint32_t)n;
+    for (int w = 0; w < W; ++w) {
+        B200PS_REQUIRE(d_ids[w], B200PS_ERR_INVALID, "ids of worker %d are null", w);
+        src.ids[w] = d_ids[w];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int launches = 0;
+    B200PS_CUDA(cudaMemsetAsync(ws.hdr, 0, HDR_WORDS * 4, st));
+
+    PassArgs a{};
+    a.hist = ws.hist;
+    a.hdr = ws.hdr;
+    a.nb = ws.nb;
+    // 1. stable partition: kept ids -> key[0], their source entry -> val[0]
+    a.key_out = ws.key[0];
+    a.val_out = ws.val[0];
+    pass_hist_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+    B200PS_CUDA(scan_exclusive(ws.hist, ws.hist, BINS * ws.nb, ws.scan_sums, st, &launches));
+    pass_scatter_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+    launches += 2;
+    // 2. LSD radix passes, ping-pong between the two buffers
+    const int passes = key_passes(g.rows);
+    int cur = 0;
+    for (int p = 0; p < passes; ++p, cur ^= 1) {
+        a.key_in = ws.key[cur];
+        a.val_in = ws.val[cur];
+        a.key_out = ws.key[cur ^ 1];
+        a.val_out = ws.val[cur ^ 1];
+        a.shift = 8 * p;
+        pass_hist_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        B200PS_CUDA(scan_exclusive(ws.hist, ws.hist, BINS * ws.nb, ws.scan_sums, st, &launches));
+        pass_scatter_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        launches += 2;
+    }
+    // 3. segments
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const uint64_t want = (n + 1 + 255) / 256;
+    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
+    heads_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, (uint32_t)n + 1);
+    B200PS_CUDA(scan_exclusive(ws.seg, ws.seg, (uint32_t)n + 1, ws.scan_sums, st, &launches));
+    segments_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, (uint32_t)n);
+    launches += 2;
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add((uint64_t)launches, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_sparse_apply_sgd(float* const* d_shard_base, const float* const* d_grad_rows, int W,
+                                       uint64_t ids_per_worker, const b200ps_table_geom_t* geom, float lr,
+                                       const void* d_workspace, void* stream) {
+    return sparse_apply<false>(d_shard_base, nullptr, d_grad_rows, W, ids_per_worker, geom, lr, d_workspace, stream);
+}
+
+extern "C" int b200ps_sparse_apply_adagrad(float* const* d_shard_base, float* const* d_accum_base,
+                                           const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
+                                           const b200ps_table_geom_t* geom, float lr, const void* d_workspace, void* stream) {
+    B200PS_REQUIRE(d_accum_base, B200PS_ERR_INVALID, "Adagrad needs the accumulator shards");
+    return sparse_apply<true>(d_shard_base, d_accum_base, d_grad_rows, W, ids_per_worker, geom, lr, d_workspace, stream);
+}
+
+extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t rows, uint64_t* n_kept,
+                                       uint64_t* n_unique, uint64_t* n_bad, int64_t* h_sorted_ids, uint32_t* h_perm,
+                                       int32_t* h_seg_id, int64_t* h_unique_ids, uint32_t* h_seg_offset, void* stream) {
+    B200PS_REQUIRE(d_workspace && n_total >= 1 && rows >= 1, B200PS_ERR_INVALID, "null workspace or empty plan");
+    cudaStream_t st = (cudaStream_t)stream;
+    const Workspace ws = carve(const_cast<void*>(d_workspace), n_total);
+    uint32_t hdr[HDR_WORDS];
+    B200PS_CUDA(cudaMemcpyAsync(hdr, ws.hdr, sizeof hdr, cudaMemcpyDeviceToHost, st));
+    B200PS_CUDA(cudaStreamSynchronize(st));
+    const uint32_t kept = hdr[HDR_KEPT], uniq = hdr[HDR_UNIQUE];
+    if (n_kept) *n_kept = kept;
+    if (n_unique) *n_unique = uniq;
+    if (n_bad) *n_bad = hdr[HDR_BAD];
+    const int fin = (key_passes(rows)) & 1;  // partition wrote buffer 0, each pass flips
+    std::vector<uint32_t> tmp(kept > uniq + 1 ? kept : uniq + 1);
+    if (h_sorted_ids && kept) {
+        B200PS_CUDA(cudaMemcpyAsync(tmp.data(), ws.key[fin], kept * 4ull, cudaMemcpyDeviceToHost, st));
+        B200PS_CUDA(cudaStreamSynchronize(st));
+        for (uint32_t k = 0; k < kept; ++k) h_sorted_ids[k] = (int64_t)tmp[k];
+    }
+    if (h_perm && kept) B200PS_CUDA(cudaMemcpyAsync(h_perm, ws.val[fin], kept * 4ull, cudaMemcpyDeviceToHost, st));
+    if (h_seg_id && kept) B200PS_CUDA(cudaMemcpyAsync(h_seg_id, ws.seg, kept * 4ull, cudaMemcpyDeviceToHost, st));
+    if (h_seg_offset) B200PS_CUDA(cudaMemcpyAsync(h_seg_offset, ws.seg_off, (uniq + 1) * 4ull, cudaMemcpyDeviceToHost, st));
+    B200PS_CUDA(cudaStreamSynchronize(st));
+    if (h_unique_ids && uniq) {
+        B200PS_CUDA(cudaMemcpyAsync(tmp.data(), ws.unique, uniq * 4ull, cudaMemcpyDeviceToHost, st));
+        B200PS_CUDA(cudaStreamSynchronize(st));
+        for (uint32_t k = 0; k < uniq; ++k) h_unique_ids[k] = (int64_t)tmp[k];
+    }
+    return B200PS_OK;
+}

@@ -62,3 +62,75 @@ def set_dense_tuning(threads: int = 0, ctas_per_sm: int = 0, unroll: int = 0) ->
 
 def launch_count() -> int:
     return int(lib.b200ps_launch_count())
+
+
+# ---- sparse group (a10..a12) ---------------------------------------------------------------------
+from ._lib import TableGeom  # noqa: E402
+
+import numpy as np  # noqa: E402
+
+
+def table_geom(rows: int, dim: int, nshards: int, rank: int = 0, world: int = 1) -> TableGeom:
+    return TableGeom(rows, dim, nshards, rank, world)
+
+
+def _dev(t: torch.Tensor, dtype, name: str) -> int:
+    if not (t.is_cuda and t.dtype == dtype and t.is_contiguous()):
+        raise TypeError(f"{name} must be a contiguous {dtype} CUDA tensor (no CPU fallback exists)")
+    return t.data_ptr()
+
+
+def _ptr_or_int(x, dtype, name):
+    return x if isinstance(x, int) else _dev(x, dtype, name)
+
+
+def sparse_gather(out: torch.Tensor, shards: Sequence, geom: TableGeom, ids: torch.Tensor) -> torch.Tensor:
+    """out[k, :] = table[ids[k], :]; `shards[s]` is shard s (tensor or raw peer pointer)."""
+    sb = _ptr_array([_ptr_or_int(t, torch.float32, "shard") for t in shards])
+    check(lib.b200ps_sparse_gather(_dev(out, torch.float32, "out"), sb, C.byref(geom), _dev(ids, torch.int64, "ids"),
+                                   ids.numel(), _stream()))
+    return out
+
+
+def sparse_workspace(n_total: int) -> torch.Tensor:
+    """Scratch for one push of n_total = W * ids_per_worker entries."""
+    return torch.empty(int(lib.b200ps_sparse_workspace_bytes(n_total)), dtype=torch.uint8, device="cuda")
+
+
+def sparse_sort_segment(ids: Sequence, ids_per_worker: int, geom: TableGeom, workspace: torch.Tensor) -> None:
+    ip = _ptr_array([_ptr_or_int(t, torch.int64, "ids") for t in ids])
+    check(lib.b200ps_sparse_sort_segment(ip, len(ids), ids_per_worker, C.byref(geom), workspace.data_ptr(),
+                                         workspace.numel(), _stream()))
+
+
+def sparse_apply_sgd(shards: Sequence, grad_rows: Sequence, ids_per_worker: int, geom: TableGeom, lr: float,
+                     workspace: torch.Tensor) -> None:
+    sb = _ptr_array([_ptr_or_int(t, torch.float32, "shard") if t is not None else 0 for t in shards])
+    gp = _ptr_array([_ptr_or_int(t, torch.float32, "grad_rows") for t in grad_rows])
+    check(lib.b200ps_sparse_apply_sgd(sb, gp, len(grad_rows), ids_per_worker, C.byref(geom), lr, workspace.data_ptr(),
+                                      _stream()))
+
+
+def sparse_apply_adagrad(shards: Sequence, accums: Sequence, grad_rows: Sequence, ids_per_worker: int, geom: TableGeom,
+                         lr: float, workspace: torch.Tensor) -> None:
+    sb = _ptr_array([_ptr_or_int(t, torch.float32, "shard") if t is not None else 0 for t in shards])
+    ab = _ptr_array([_ptr_or_int(t, torch.float32, "accum") if t is not None else 0 for t in accums])
+    gp = _ptr_array([_ptr_or_int(t, torch.float32, "grad_rows") for t in grad_rows])
+    check(lib.b200ps_sparse_apply_adagrad(sb, ab, gp, len(grad_rows), ids_per_worker, C.byref(geom), lr,
+                                          workspace.data_ptr(), _stream()))
+
+
+def sparse_plan_read(workspace: torch.Tensor, n_total: int, rows: int) -> dict:
+    """The plan of the last sort_segment as NumPy arrays (debug accessor; synchronises)."""
+    kept, uniq, bad = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    s = np.empty(n_total, np.int64)
+    perm = np.empty(n_total, np.uint32)
+    seg = np.empty(n_total, np.int32)
+    un = np.empty(n_total, np.int64)
+    off = np.empty(n_total + 1, np.uint32)
+    check(lib.b200ps_sparse_plan_read(workspace.data_ptr(), n_total, rows, C.byref(kept), C.byref(uniq), C.byref(bad),
+                                      s.ctypes.data, perm.ctypes.data, seg.ctypes.data, un.ctypes.data, off.ctypes.data,
+                                      _stream()))
+    k, u = kept.value, uniq.value
+    return {"n_kept": k, "n_unique": u, "n_bad": bad.value, "sorted_ids": s[:k], "perm": perm[:k], "seg_id": seg[:k],
+            "unique_ids": un[:u], "seg_offset": off[:u + 1]}

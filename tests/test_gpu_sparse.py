@@ -1,0 +1,187 @@
+"""GPU parity of the sparse PS path (a10..a12) against the oracle, through the C ABI.
+Integer outputs (sorted ids, permutation, segment ids, unique ids, offsets) and the updated rows
+are BIT-EXACT."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+import b200ps
+from b200ps import kernels as K
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def make_ids(rng, kind, W, B, rows):
+    if kind == "uniform":
+        return rng.integers(0, rows, (W, B))
+    if kind == "zipf":
+        return np.minimum(rng.zipf(1.05, (W, B)) - 1, rows - 1)
+    if kind == "one_hot_row":
+        return np.full((W, B), rows // 2)
+    if kind == "distinct":
+        return rng.permutation(rows)[: W * B].reshape(W, B)
+    raise ValueError(kind)
+
+
+def shard_views(table, rows, S):
+    """Per-shard tensors over one contiguous table (div partition)."""
+    return [table[slice(*b200ps.row_range(rows, S, s))] for s in range(S)]
+
+
+@pytest.mark.parametrize("rows,S,dim,W,B,kind", [
+    (10, 1, 4, 1, 4, "uniform"),
+    (1000, 3, 64, 4, 257, "uniform"),
+    (100_000, 8, 64, 8, 4096, "uniform"),
+    (100_000, 8, 64, 8, 4096, "zipf"),
+    (5_000, 4, 8, 2, 3000, "one_hot_row"),
+    (70_000, 5, 128, 3, 5000, "distinct"),
+    (300, 7, 16, 5, 1, "uniform"),
+    (1 << 20, 2, 32, 2, 50_000, "zipf"),
+])
+def test_sort_segment_bit_exact(oracle, rows, S, dim, W, B, kind):
+    rng = np.random.default_rng(rows + W + B)
+    ids = make_ids(rng, kind, W, B, rows).astype(np.int64)
+    dids = [dev(ids[w]) for w in range(W)]
+    ws = K.sparse_workspace(W * B)
+    geom = K.table_geom(rows, dim, S)
+    K.sparse_sort_segment(dids, B, geom, ws)
+    plan = K.sparse_plan_read(ws, W * B, rows)
+    s, perm, seg, uniq, off = oracle.sort_segment(ids.reshape(-1))
+    assert plan["n_kept"] == W * B and plan["n_unique"] == len(uniq) and plan["n_bad"] == 0
+    assert np.array_equal(plan["sorted_ids"], s)
+    assert np.array_equal(plan["perm"], perm)
+    assert np.array_equal(plan["seg_id"], seg)
+    assert np.array_equal(plan["unique_ids"], uniq)
+    assert np.array_equal(plan["seg_offset"], off)
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adagrad"])
+@pytest.mark.parametrize("rows,S,dim,W,B,kind", [
+    (1000, 3, 64, 4, 257, "uniform"),
+    (50_000, 8, 64, 8, 2048, "zipf"),
+    (2_000, 4, 8, 2, 1500, "one_hot_row"),
+    (20_000, 5, 128, 3, 2000, "distinct"),
+    (64, 2, 4, 2, 100, "uniform"),
+])
+def test_push_apply_bit_exact_over_steps(oracle, opt, rows, S, dim, W, B, kind):
+    rng = np.random.default_rng(7 * rows + B)
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+    accum = np.full((rows, dim), 0.1, np.float32)
+    dt, da = dev(table), dev(accum)
+    geom = K.table_geom(rows, dim, S)
+    ws = K.sparse_workspace(W * B)
+    inv_w = np.float32(1.0) / np.float32(W)
+    for step in range(3):
+        ids = make_ids(rng, kind, W, B, rows).astype(np.int64)
+        grad = oracle.fill_uniform(W * B * dim, 2, step + 1, 0).reshape(W * B, dim)
+        dids = [dev(ids[w]) for w in range(W)]
+        dgr = [dev(grad[w * B:(w + 1) * B]) for w in range(W)]
+        K.sparse_sort_segment(dids, B, geom, ws)
+        if opt == "sgd":
+            K.sparse_apply_sgd(shard_views(dt, rows, S), dgr, B, geom, 0.05, ws)
+            oracle.sparse_apply_sgd(table, 0, grad, ids.reshape(-1), inv_w, np.float32(0.05))
+        else:
+            K.sparse_apply_adagrad(shard_views(dt, rows, S), shard_views(da, rows, S), dgr, B, geom, 0.05, ws)
+            oracle.sparse_apply_adagrad(table, accum, 0, grad, ids.reshape(-1), inv_w, np.float32(0.05))
+    assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
+    if opt == "adagrad":
+        assert np.array_equal(da.cpu().numpy().view(np.uint32), accum.view(np.uint32))
+
+
+@pytest.mark.parametrize("rows,S,dim,n", [(10, 1, 4, 7), (1000, 3, 64, 5000), (100_003, 8, 64, 100_000), (777, 5, 256, 300)])
+def test_gather_exact_copies(oracle, rows, S, dim, n):
+    rng = np.random.default_rng(n)
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+    ids = rng.integers(0, rows, n).astype(np.int64)
+    dt = dev(table)
+    out = torch.empty(n, dim, dtype=torch.float32, device="cuda")
+    K.sparse_gather(out, shard_views(dt, rows, S), K.table_geom(rows, dim, S), dev(ids))
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.gather(table, ids).view(np.uint32))
+
+
+def test_partition_keeps_only_this_gpus_shards(oracle):
+    """world > 1 on one device: each 'rank' keeps exactly the ids of its shards, in order; the
+    union of the ranks' updates equals the single-rank update."""
+    rows, S, dim, W, B, world = 10_000, 8, 16, 4, 3000, 4
+    rng = np.random.default_rng(11)
+    ids = rng.integers(0, rows, (W, B)).astype(np.int64)
+    grad = oracle.fill_uniform(W * B * dim, 2, 1, 0).reshape(W * B, dim)
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+    dt = dev(table)
+    dids, dgr = [dev(ids[w]) for w in range(W)], [dev(grad[w * B:(w + 1) * B]) for w in range(W)]
+    ws = K.sparse_workspace(W * B)
+    owners = np.array([oracle.row_owner(rows, S, int(i)) for i in ids.reshape(-1)])
+    total_kept = 0
+    for rank in range(world):
+        geom = K.table_geom(rows, dim, S, rank, world)
+        K.sparse_sort_segment(dids, B, geom, ws)
+        plan = K.sparse_plan_read(ws, W * B, rows)
+        mine = np.flatnonzero(owners % world == rank)
+        s, perm, seg, uniq, off = oracle.sort_segment(ids.reshape(-1)[mine])
+        assert plan["n_kept"] == len(mine)
+        assert np.array_equal(plan["sorted_ids"], s) and np.array_equal(plan["perm"], mine[perm])
+        assert np.array_equal(plan["seg_id"], seg) and np.array_equal(plan["seg_offset"], off)
+        total_kept += plan["n_kept"]
+        K.sparse_apply_sgd(shard_views(dt, rows, S), dgr, B, geom, 0.1, ws)
+    assert total_kept == W * B
+    oracle.sparse_apply_sgd(table, 0, grad, ids.reshape(-1), np.float32(0.25), np.float32(0.1))
+    assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
+
+
+def test_out_of_range_ids_are_dropped_and_counted(oracle):
+    rows, S, dim = 100, 2, 4
+    ids = np.array([[5, -1, 100, 7, 5, 1 << 40]], np.int64)
+    ws = K.sparse_workspace(ids.size)
+    K.sparse_sort_segment([dev(ids[0])], ids.shape[1], K.table_geom(rows, dim, S), ws)
+    plan = K.sparse_plan_read(ws, ids.size, rows)
+    assert plan["n_bad"] == 3 and plan["sorted_ids"].tolist() == [5, 5, 7] and plan["perm"].tolist() == [0, 4, 3]
+    out = torch.full((6, dim), 9.0, device="cuda")
+    t = torch.ones(rows, dim, device="cuda")
+    K.sparse_gather(out, shard_views(t, rows, S), K.table_geom(rows, dim, S), dev(ids[0]))
+    assert out.sum(1).tolist() == [4.0, 0.0, 0.0, 4.0, 4.0, 0.0]
+
+
+def test_argument_errors():
+    ws = K.sparse_workspace(8)
+    ids = torch.zeros(8, dtype=torch.int64, device="cuda")
+    with pytest.raises(b200ps.B200PSError):
+        K.sparse_sort_segment([ids], 8, K.table_geom(100, 6, 1), ws)  # dim not a multiple of 4
+    with pytest.raises(b200ps.B200PSError):
+        K.sparse_sort_segment([ids], 8, K.table_geom(1 << 33, 4, 1), ws)  # rows >= 2^32
+    with pytest.raises(b200ps.B200PSError, match="too small"):
+        K.sparse_sort_segment([ids] * 4, 8, K.table_geom(100, 4, 1), ws)
+    with pytest.raises(b200ps.B200PSError):
+        K.sparse_sort_segment([ids], 8, K.table_geom(100, 4, 2, 2, 2), ws)  # rank outside world
+
+
+def test_c2_shapes_full_batch(oracle):
+    """BASELINE configs[2] geometry at a table size the oracle sorts in seconds: 8 shards, 8
+    workers, 262 144 ids per worker, dim 64, Zipf(1.05) ids; sortedness / conservation properties
+    at full batch plus bit-exact rows."""
+    rows, S, dim, W, B = 1_000_000, 8, 64, 8, 262_144
+    rng = np.random.default_rng(5)
+    ids = np.minimum(rng.zipf(1.05, (W, B)) - 1, rows - 1).astype(np.int64)
+    dids = [dev(ids[w]) for w in range(W)]
+    geom = K.table_geom(rows, dim, S)
+    ws = K.sparse_workspace(W * B)
+    K.sparse_sort_segment(dids, B, geom, ws)
+    plan = K.sparse_plan_read(ws, W * B, rows)
+    s = plan["sorted_ids"]
+    assert plan["n_kept"] == W * B and (np.diff(s) >= 0).all()                      # sorted
+    assert np.array_equal(np.sort(plan["perm"]), np.arange(W * B, dtype=np.uint32))   # a permutation
+    assert np.array_equal(ids.reshape(-1)[plan["perm"]], s)                           # of the input
+    same = s[1:] == s[:-1]
+    assert (np.diff(plan["perm"].astype(np.int64))[same] > 0).all()                   # stable
+    assert plan["n_unique"] == len(np.unique(ids)) and plan["seg_offset"][-1] == W * B
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0, threads=8).reshape(rows, dim)
+    grad = oracle.fill_uniform(W * B * dim, 2, 1, 0, threads=8).reshape(W * B, dim)
+    dt = dev(table)
+    dgr = [dev(grad[w * B:(w + 1) * B]) for w in range(W)]
+    K.sparse_apply_sgd(shard_views(dt, rows, S), dgr, B, geom, 0.05, ws)
+    oracle.sparse_apply_sgd(table, 0, grad, ids.reshape(-1), np.float32(1.0) / np.float32(W), np.float32(0.05))
+    assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))

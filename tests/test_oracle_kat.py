@@ -144,3 +144,19 @@ def test_bucket_by_owner(oracle):
     perm, off = oracle.bucket_by_owner(ids, 10, 4)
     assert off.tolist() == [0, 2, 4, 5, 7]
     assert perm.tolist() == [1, 5, 2, 3, 6, 0, 4]  # stable inside each bucket
+
+
+def test_long_segment_chunked_fold(oracle, nporacle):
+    """Hot ids: a segment longer than 256 entries is folded chunk-wise; C and NumPy agree, and the
+    result differs from a naive left fold only in rounding."""
+    rng = np.random.default_rng(3)
+    n, dim = 1000, 4
+    ids = np.concatenate([np.full(700, 7), rng.integers(0, 20, n - 700)])
+    rng.shuffle(ids)
+    grad = rng.uniform(-1, 1, (n, dim)).astype(np.float32)
+    t0 = rng.uniform(-1, 1, (20, dim)).astype(np.float32)
+    a = oracle.sparse_apply_sgd(t0.copy(), 0, grad, ids, np.float32(0.125), np.float32(0.5))
+    b = nporacle.sparse_apply_sgd(t0.copy(), 0, grad, ids, np.float32(0.125), np.float32(0.5))
+    assert np.array_equal(a, b)
+    naive = t0[7].astype(np.float64) - 0.5 * 0.125 * grad[ids == 7].astype(np.float64).sum(0)
+    assert np.allclose(a[7], naive, rtol=1e-4, atol=1e-5)
