@@ -153,8 +153,9 @@ def test_argument_errors():
         K.sparse_sort_segment([ids], 8, K.table_geom(100, 6, 1), ws)  # dim not a multiple of 4
     with pytest.raises(b200ps.B200PSError):
         K.sparse_sort_segment([ids], 8, K.table_geom(1 << 33, 4, 1), ws)  # rows >= 2^32
+    big = torch.zeros(4096, dtype=torch.int64, device="cuda")
     with pytest.raises(b200ps.B200PSError, match="too small"):
-        K.sparse_sort_segment([ids] * 4, 8, K.table_geom(100, 4, 1), ws)
+        K.sparse_sort_segment([big] * 4, 4096, K.table_geom(100, 4, 1), ws)
     with pytest.raises(b200ps.B200PSError):
         K.sparse_sort_segment([ids], 8, K.table_geom(100, 4, 2, 2, 2), ws)  # rank outside world
 
