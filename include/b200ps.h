@@ -206,6 +206,35 @@ int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t 
                             uint64_t* n_unique, uint64_t* n_bad, int64_t* h_sorted_ids, uint32_t* h_perm,
                             int32_t* h_seg_id, int64_t* h_unique_ids, uint32_t* h_seg_offset, void* stream);
 
+/* No counterpart in the reference (nor in TensorFlow's PS ops): an entry point for callers that
+ * must not allocate device memory.
+ *
+ * One whole sparse push with SGD -- exactly b200ps_sparse_sort_segment followed by
+ * b200ps_sparse_apply_sgd -- whose workspace is a fixed array inside the library instead of
+ * memory the caller provides.  It calls no cudaMalloc / cudaFree and no allocating library
+ * routine; the caller passes only its inputs (ids, gradient rows) and the table shards it updates.
+ * It is meant for a task whose HBM share was given out completely at launch (shards, gradient
+ * buffers and replicas are sized to fill the GPU, so a later cudaMalloc can fail), and for a step
+ * loop with push / apply / pull in flight on several streams, which cudaMalloc or cudaFree would
+ * stall because they synchronise the whole device.
+ *
+ *  - limit: W * ids_per_worker <= B200PS_NOALLOC_MAX_ENTRIES; larger pushes are rejected with
+ *    B200PS_ERR_RANGE (use the two-call form with your own workspace).
+ *  - cost: every GPU this process uses the library on holds B200PS_NOALLOC_SCRATCH_BYTES of
+ *    device memory for the array until the process exits.
+ *  - the first call on each device looks up the array's device address (with that device
+ *    current); make that first call before any stream capture begins.
+ *  - the array is shared by all calls on a device and keeps the previous call's contents; the
+ *    words that must start at zero are cleared on `stream` at the start of each call.  Two calls
+ *    that can overlap on the GPU (different streams, no ordering between them) race on it:
+ *    order them on one stream or with events.
+ */
+#define B200PS_NOALLOC_MAX_ENTRIES 262144ull
+#define B200PS_NOALLOC_SCRATCH_BYTES 7864320ull /* 7.5 MiB, >= the plan of MAX_ENTRIES entries */
+int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const int64_t* const* d_ids,
+                                   const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
+                                   const b200ps_table_geom_t* geom, float lr, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,6 +80,7 @@ SIGNATURES = {
     "b200ps_sparse_sort_segment": (_i32, [_vp, _i32, _u64, C.POINTER(TableGeom), _vp, _sz, _vp]),
     "b200ps_sparse_apply_sgd": (_i32, [_vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp, _vp]),
     "b200ps_sparse_apply_adagrad": (_i32, [_vp, _vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp, _vp]),
+    "b200ps_sparse_push_sgd_noalloc": (_i32, [_vp, _vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp]),
     "b200ps_sparse_plan_read": (_i32, [_vp, _u64, _u64, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64), _vp, _vp, _vp,
                                         _vp, _vp, _vp]),
 }

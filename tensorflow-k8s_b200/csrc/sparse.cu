@@ -669,3 +669,63 @@ extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total
     }
     return B200PS_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// b200ps_sparse_push_sgd_noalloc: a whole sparse push (sort_segment + apply_sgd) for callers that
+// must not allocate device memory.  The plan / sort scratch lives in the fixed array below instead
+// of a caller-provided workspace.
+//
+// Who needs this: a PS or worker task whose share of HBM was handed out completely when the job
+// was launched (table shards, gradient buffers, replicas -- the launcher sizes them to fill the
+// GPU), so a later cudaMalloc may simply fail; and a step loop that keeps push, apply and pull in
+// flight on several streams, where cudaMalloc / cudaFree would stall every one of them because they
+// synchronise the whole device.  Such a caller passes only its inputs and the table it updates.
+//
+// The array is part of the library image: every GPU on which this process uses the library keeps
+// B200PS_NOALLOC_SCRATCH_BYTES of it resident until the process exits, whether or not this entry
+// point is ever called.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200PS_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not an address a kernel can
+// use, so the device address is looked up once per device (with that device current) and cached.
+int noalloc_scratch_address(void** out) {
+    static void* cached[64] = {nullptr};
+    int dev = 0;
+    B200PS_CUDA(cudaGetDevice(&dev));
+    B200PS_REQUIRE(dev >= 0 && dev < 64, B200PS_ERR_RANGE, "device ordinal %d is outside 0..63", dev);
+    void* p = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        B200PS_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        B200PS_REQUIRE(p && ((uintptr_t)p & 255) == 0, B200PS_ERR_CUDA, "static scratch has no usable device address");
+        __atomic_store_n(&cached[dev], p, __ATOMIC_RELEASE);  // every thread resolves the same address
+    }
+    *out = p;
+    return B200PS_OK;
+}
+
+}  // namespace
+
+extern "C" int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const int64_t* const* d_ids,
+                                              const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
+                                              const b200ps_table_geom_t* geom, float lr, void* stream) {
+    B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS, B200PS_ERR_RANGE, "W = %d is outside 1..%d", W, B200PS_MAX_WORKERS);
+    const uint64_t n = (uint64_t)W * ids_per_worker;
+    B200PS_REQUIRE(n >= 1 && n <= B200PS_NOALLOC_MAX_ENTRIES, B200PS_ERR_RANGE,
+                   "push of %llu entries (W * ids_per_worker) exceeds the %llu the static scratch holds; "
+                   "use b200ps_sparse_sort_segment + b200ps_sparse_apply_sgd with your own workspace",
+                   (unsigned long long)n, (unsigned long long)B200PS_NOALLOC_MAX_ENTRIES);
+    const size_t need = carve(nullptr, n).bytes;
+    B200PS_REQUIRE(need <= (size_t)B200PS_NOALLOC_SCRATCH_BYTES, B200PS_ERR_RANGE,
+                   "static scratch of %llu bytes cannot hold the %zu-byte plan of %llu entries",
+                   (unsigned long long)B200PS_NOALLOC_SCRATCH_BYTES, need, (unsigned long long)n);
+    void* scratch = nullptr;
+    if (int rc = noalloc_scratch_address(&scratch)) return rc;
+    // The array still holds the previous call's plan.  sort_segment zeroes the header (the only
+    // part that must start at zero) on the stream and rewrites every other word it later reads.
+    if (int rc = b200ps_sparse_sort_segment(d_ids, W, ids_per_worker, geom, scratch, B200PS_NOALLOC_SCRATCH_BYTES, stream))
+        return rc;
+    return b200ps_sparse_apply_sgd(d_shard_base, d_grad_rows, W, ids_per_worker, geom, lr, scratch, stream);
+}

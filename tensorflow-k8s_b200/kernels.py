@@ -134,3 +134,20 @@ def sparse_plan_read(workspace: torch.Tensor, n_total: int, rows: int) -> dict:
     k, u = kept.value, uniq.value
     return {"n_kept": k, "n_unique": u, "n_bad": bad.value, "sorted_ids": s[:k], "perm": perm[:k], "seg_id": seg[:k],
             "unique_ids": un[:u], "seg_offset": off[:u + 1]}
+
+
+NOALLOC_MAX_ENTRIES = 262144  # B200PS_NOALLOC_MAX_ENTRIES
+
+
+def sparse_push_sgd_noalloc(shards: Sequence, ids: Sequence, grad_rows: Sequence, ids_per_worker: int, geom: TableGeom,
+                            lr: float) -> None:
+    """A whole sparse SGD push (sort_segment + apply_sgd) that allocates nothing on the device:
+    for tasks whose HBM is fully handed out at launch and for step loops that cannot afford the
+    device-wide stall of cudaMalloc.  The scratch is a fixed array inside the library, so W *
+    ids_per_worker is limited to NOALLOC_MAX_ENTRIES, and calls that may overlap on the GPU must
+    be ordered by the caller (they share the array).  Make the first call before any stream
+    capture."""
+    sb = _ptr_array([_ptr_or_int(t, torch.float32, "shard") if t is not None else 0 for t in shards])
+    ip = _ptr_array([_ptr_or_int(t, torch.int64, "ids") for t in ids])
+    gp = _ptr_array([_ptr_or_int(t, torch.float32, "grad_rows") for t in grad_rows])
+    check(lib.b200ps_sparse_push_sgd_noalloc(sb, ip, gp, len(ids), ids_per_worker, C.byref(geom), lr, _stream()))
