@@ -36,7 +36,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200ps", choices=["b200ps", "reference"])
-    ap.add_argument("--workload", default="c1", choices=["c0", "c1", "c3"])
+    ap.add_argument("--workload", default="c1", choices=["c0", "c1", "c2", "c3"])
+    ap.add_argument("--ids", default="zipf", choices=["zipf", "uniform"], help="id distribution of --workload c2")
+    ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true")
@@ -176,9 +178,186 @@ def reference_arm(args):
     }))
 
 
+# ------------------------------------------------------------------------------------------------ sparse (C2)
+C2 = dict(dim=64, S=8, W=8, B=262_144, lr=0.05)
+
+
+def sparse_cpu(rows, ids_kind, steps, seconds):
+    """Oracle on the host: per step W gathers + sort_segment + SGD apply (single thread: the
+    restatement of the sparse path is scalar)."""
+    import numpy as np
+
+    from b200ps import synth
+    from oracle import c_oracle as O
+
+    dim, W, B = C2["dim"], C2["W"], C2["B"]
+    table = O.fill_uniform(rows * dim, 1, 0, 0, threads=O.max_threads()).reshape(rows, dim)
+    grad = O.fill_uniform(W * B * dim, 2, 1, 0, threads=O.max_threads()).reshape(W * B, dim)
+    ids = synth.make_ids(ids_kind, rows, W, B, 1)
+    t0, done = time.perf_counter(), 0
+    while done < steps:
+        for w in range(W):
+            O.gather(table, ids[w])
+        O.sparse_apply_sgd(table, 0, grad, ids.reshape(-1), np.float32(1.0) / np.float32(W), np.float32(C2["lr"]))
+        done += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    dt = time.perf_counter() - t0
+    return W * done / dt, done, 1e3 * dt / done
+
+
+def sparse_arm(args):
+    """--workload c2: Wide&Deep embedding table 10M x 64 over 8 PS shards, 8 workers, 262144 ids per
+    worker per step; a step = every worker pulls its rows (a10) + one push (a11 + a12)."""
+    rank = int(os.environ.get("RANK", "0"))
+    rows, dim, S, W, B = args.rows, C2["dim"], C2["S"], C2["W"], C2["B"]
+    label = f"C2 Wide&Deep embedding {rows}x{dim}, {S} PS shards, {W} workers, {B} ids/worker/step, {args.ids} ids, SGD"
+    if args.impl == "reference":
+        if rank == 0:
+            val, done, ms = sparse_cpu(rows, args.ids, args.steps, 120.0)
+            print(json.dumps({"impl": "reference", "metric": "ps_steps_per_sec", "value": round(val, 3), "unit": "worker-steps/s",
+                              "n_gpus": args.gpus, "steps": done, "warmup": 0, "ms_per_step": round(ms, 2),
+                              "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32+i64",
+                              "data": "synthetic", "config": {"workload": label},
+                              "cpu_baseline": {"value": round(val, 3), "unit": "worker-steps/s", "cores": 1, "kind": "port",
+                                               "sample": f"{done} full steps; substitute CPU reference (oracle/ps_oracle.c, scalar)"},
+                              "e2e": {"value": round(val, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 0,
+                                      "d2h_bytes_per_step": 0}}))
+        return
+    import torch
+    import torch.distributed as dist
+
+    import b200ps
+    from b200ps import kernels as K, synth
+
+    world, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd", lr=C2["lr"], rank=rank, world=world)
+    tab.init_uniform(1)
+    ids = synth.make_ids(args.ids, rows, W, B, 1)
+    outs = {}
+    for w in tab.local_workers:
+        tab.ids[w].copy_(torch.from_numpy(ids[w]))
+        K.fill_uniform(tab.grad_rows[w].view(-1), 2, 1, 0, first=w * B * dim)
+        outs[w] = torch.empty(B, dim, dtype=torch.float32, device="cuda")
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step(ev=None):
+        if ev:
+            ev[0].record()
+        for w in tab.local_workers:
+            tab.pull(w, outs[w])
+        if ev:
+            ev[1].record()
+        tab._barrier()
+        tab.sort_segment()
+        if ev:
+            ev[2].record()
+        tab.apply()
+        if ev:
+            ev[3].record()
+        tab._barrier()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync()
+    plan = tab.plan()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = K.launch_count()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(args.steps):
+        step(evs[i])
+    b.record()
+    sync()
+    clocks = sampler.finish()
+    launches = K.launch_count() - l0
+    ms = a.elapsed_time(b) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    g_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    s_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+    p_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
+    d4 = 4 * dim
+    gather_bytes = len(tab.local_workers) * B * (8 + 2 * d4)
+    apply_bytes = plan["n_kept"] * (4 + d4) + plan["n_unique"] * (2 * d4 + 4)  # perm + rows; unique id + row R/W
+    peak, peak_src = hbm_peak()
+    e2e = None
+    if not args.no_e2e:
+        # host buffers: ids + gradient rows of every local worker go H2D, the pulled rows come back D2H
+        h_ids = {w: torch.from_numpy(ids[w]).pin_memory() for w in tab.local_workers}
+        h_gr = {w: torch.empty(B, dim, dtype=torch.float32).pin_memory() for w in tab.local_workers}
+        h_out = {w: torch.empty(B, dim, dtype=torch.float32).pin_memory() for w in tab.local_workers}
+        for w in tab.local_workers:
+            h_gr[w].copy_(tab.grad_rows[w])
+
+        def host_step():
+            for w in tab.local_workers:
+                tab.ids[w].copy_(h_ids[w], non_blocking=True)
+                tab.grad_rows[w].copy_(h_gr[w], non_blocking=True)
+            for w in tab.local_workers:
+                tab.pull(w, outs[w])
+                h_out[w].copy_(outs[w], non_blocking=True)
+            tab.push_step()
+
+        for _ in range(3):
+            host_step()
+        sync()
+        n_e = min(args.steps, 30)
+        a.record()
+        for _ in range(n_e):
+            host_step()
+        b.record()
+        sync()
+        e_ms = a.elapsed_time(b) / n_e
+        e2e = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": W * B * (8 + d4),
+               "d2h_bytes_per_step": W * B * d4, "ms_per_step": round(e_ms, 3), "steps": n_e,
+               "api": "b200ps.EmbeddingTable: ids + gradient rows H2D, pull -> D2H, push_step"}
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        tab.close()
+        torch.cuda.empty_cache()
+        val, done, cms = sparse_cpu(rows, args.ids, 10 ** 6, args.cpu_seconds)
+        cpu = {"value": round(val, 3), "unit": "worker-steps/s", "cores": 1, "kind": "port",
+               "sample": f"{done} full steps ({cms:.0f} ms each); substitute CPU reference (oracle/ps_oracle.c, scalar sparse path)"}
+    if rank == 0:
+        print(json.dumps({
+            "metric": "ps_steps_per_sec", "value": round(W * 1e3 / ms, 3), "unit": "worker-steps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
+            "config": {"workload": label, "n_kept": int(plan["n_kept"]), "n_unique": int(plan["n_unique"]),
+                       "longest_segment": int(plan["seg_offset"][1:].astype("int64").__sub__(plan["seg_offset"][:-1]).max()),
+                       "l2": "table 2.56 GB and 0.54 GB of gradient rows per step exceed L2; no flush"},
+            "ps_steps_per_sec": round(1e3 / ms, 3),
+            "phases_ms": {"gather_all_local_workers": round(g_ms, 4), "sort_segment": round(s_ms, 4), "apply": round(p_ms, 4)},
+            "roofline": {"bound": "hbm", "achieved": round(gather_bytes / g_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(gather_bytes / g_ms / 1e6 / peak, 4), "traffic": None, "kernel": "sparse_gather_kernel<16>",
+                         "peak_source": peak_src, "algorithmic_bytes_per_step": gather_bytes},
+            "roofline_apply": {"bound": "hbm", "achieved": round(apply_bytes / p_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
+                               "frac": round(apply_bytes / p_ms / 1e6 / peak, 4), "kernel": "sparse_apply_kernel<16,sgd>",
+                               "algorithmic_bytes_per_step": int(apply_bytes)},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------------ GPU arm
 def main():
     args = parse()
+    if args.workload == "c2":
+        return sparse_arm(args)
     if args.impl == "reference":
         return reference_arm(args)
 

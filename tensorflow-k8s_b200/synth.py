@@ -39,3 +39,30 @@ def resnet50_c3_variables() -> List[int]:
 def sweep_c4_sizes() -> List[int]:
     """C4: 1 KB ... 1 GB in powers of 4 (fp32 element counts)."""
     return [256 * 4 ** k for k in range(11)]
+
+
+def make_ids(kind: str, rows: int, workers: int, per_worker: int, step: int = 1, seed: int = SEED_IDS):
+    """Embedding ids int64 [workers, per_worker]: 'uniform' over the rows, or
+    'zipf' = Zipf(1.05) by the inverse CDF of the continuous power law.  Driven by the same
+    splitmix64 counter hash as the fp32 generator, so the arrays are reproducible everywhere;
+    they are INPUTS (fed identically to the GPU path and to the checker)."""
+    import numpy as np
+
+    u64 = np.uint64
+    idx = np.arange(workers * per_worker, dtype=np.uint64)
+    key = ((seed * 0xD6E8FEB86659FD93) ^ (step * 0xA24BAED4963EE407)) & ((1 << 64) - 1)
+    with np.errstate(over="ignore"):
+        z = (idx ^ u64(key)) + u64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> u64(30))) * u64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> u64(27))) * u64(0x94D049BB133111EB)
+        z = z ^ (z >> u64(31))
+    if kind == "uniform":
+        ids = (z % u64(rows)).astype(np.int64)
+    elif kind == "zipf":
+        alpha = 1.05
+        u = (z >> u64(11)).astype(np.float64) * 2.0 ** -53
+        x = ((float(rows) ** (1.0 - alpha) - 1.0) * u + 1.0) ** (1.0 / (1.0 - alpha))
+        ids = np.clip(np.floor(x).astype(np.int64) - 1, 0, rows - 1)
+    else:
+        raise ValueError("kind must be 'uniform' or 'zipf'")
+    return ids.reshape(workers, per_worker)

@@ -186,3 +186,33 @@ def test_c2_shapes_full_batch(oracle):
     K.sparse_apply_sgd(shard_views(dt, rows, S), dgr, B, geom, 0.05, ws)
     oracle.sparse_apply_sgd(table, 0, grad, ids.reshape(-1), np.float32(1.0) / np.float32(W), np.float32(0.05))
     assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
+
+
+@pytest.mark.parametrize("opt,kind", [("sgd", "zipf"), ("adagrad", "uniform")])
+def test_embedding_table_host_api(oracle, opt, kind):
+    """b200ps.EmbeddingTable (world = 1): pull then push for 2 steps equals the oracle bit for bit."""
+    rows, dim, S, W, B = 40_000, 64, 8, 8, 2048
+    tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer=opt, lr=0.05)
+    tab.init_uniform(1)
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+    accum = np.full((rows, dim), 0.1, np.float32)
+    out = torch.empty(B, dim, dtype=torch.float32, device="cuda")
+    for step in (1, 2):
+        ids = b200ps.synth.make_ids(kind, rows, W, B, step)
+        grad = oracle.fill_uniform(W * B * dim, 2, step, 0).reshape(W, B, dim)
+        for w in range(W):
+            tab.ids[w].copy_(torch.from_numpy(ids[w]))
+            tab.grad_rows[w].copy_(torch.from_numpy(grad[w]))
+        for w in (0, W - 1):
+            tab.pull(w, out)
+            assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.gather(table, ids[w]).view(np.uint32))
+        tab.push_step()
+        if opt == "sgd":
+            oracle.sparse_apply_sgd(table, 0, grad.reshape(-1, dim), ids.reshape(-1), np.float32(1.0) / np.float32(W), np.float32(0.05))
+        else:
+            oracle.sparse_apply_adagrad(table, accum, 0, grad.reshape(-1, dim), ids.reshape(-1), np.float32(1.0) / np.float32(W),
+                                        np.float32(0.05))
+    got = np.concatenate([v for _, (_, v) in sorted(tab.dump().items())])
+    assert np.array_equal(got.view(np.uint32), table.view(np.uint32))
+    assert tab.plan()["n_kept"] == W * B
+    tab.close()
