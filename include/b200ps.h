@@ -186,9 +186,10 @@ typedef struct {
 
 int b200ps_sparse_gather(float* d_out, const float* const* d_shard_base, const b200ps_table_geom_t* geom,
                          const int64_t* d_ids, uint64_t n, void* stream);
-/* scratch for one push of n_total = W * ids_per_worker entries (256-byte aligned device memory
- * the caller owns; contents are the plan the apply call reads) */
-size_t b200ps_sparse_workspace_bytes(uint64_t n_total);
+/* scratch for one push of n_total = W * ids_per_worker entries of a table with `dim` floats per
+ * row (256-byte aligned device memory the caller owns; it holds the plan the apply call reads,
+ * plus the per-chunk partial rows the apply call uses for ids with more than 256 entries) */
+size_t b200ps_sparse_workspace_bytes(uint64_t n_total, int dim);
 int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, uint64_t ids_per_worker,
                                const b200ps_table_geom_t* geom, void* d_workspace, size_t workspace_bytes,
                                void* stream);
@@ -218,8 +219,10 @@ int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t 
  * loop with push / apply / pull in flight on several streams, which cudaMalloc or cudaFree would
  * stall because they synchronise the whole device.
  *
- *  - limit: W * ids_per_worker <= B200PS_NOALLOC_MAX_ENTRIES; larger pushes are rejected with
- *    B200PS_ERR_RANGE (use the two-call form with your own workspace).
+ *  - limit: W * ids_per_worker <= B200PS_NOALLOC_MAX_ENTRIES, and the workspace of that push
+ *    (b200ps_sparse_workspace_bytes, which grows with dim) must fit the array -- true for every
+ *    dim <= 512 at the full entry count; anything larger is rejected with B200PS_ERR_RANGE (use
+ *    the two-call form with your own workspace).
  *  - cost: every GPU this process uses the library on holds B200PS_NOALLOC_SCRATCH_BYTES of
  *    device memory for the array until the process exits.
  *  - the first call on each device looks up the array's device address (with that device
@@ -230,7 +233,7 @@ int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t 
  *    order them on one stream or with events.
  */
 #define B200PS_NOALLOC_MAX_ENTRIES 262144ull
-#define B200PS_NOALLOC_SCRATCH_BYTES 7864320ull /* 7.5 MiB, >= the plan of MAX_ENTRIES entries */
+#define B200PS_NOALLOC_SCRATCH_BYTES 12582912ull /* 12 MiB: MAX_ENTRIES entries at dim <= 512 */
 int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const int64_t* const* d_ids,
                                    const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
                                    const b200ps_table_geom_t* geom, float lr, void* stream);

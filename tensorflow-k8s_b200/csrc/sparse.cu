@@ -42,7 +42,7 @@ constexpr int SCAN_TILE = SCAN_THREADS * 4;
 constexpr uint32_t SEG_CHUNK = 256;  // == PS_SEG_CHUNK of the oracle
 constexpr uint32_t NONE = 0xFFFFFFFFu;
 
-enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_FINAL = 3, HDR_WORDS = 64 };
+enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_NLONG = 4, HDR_NCHUNKS = 5, HDR_WORDS = 64 };
 
 struct Geom {
     uint64_t rows;
@@ -89,13 +89,20 @@ struct Workspace {
     uint32_t* seg;        // n + 1: head-count scan, then segment ids
     uint32_t* unique;     // n
     uint32_t* seg_off;    // n + 1
+    // tail, used by the apply step only (hot ids): segments longer than SEG_CHUNK
+    uint32_t* long_u;     // unique index of each long segment
+    uint32_t* long_base;  // its first chunk in `chunks` / `partials`
+    uint2* chunks;        // (unique index, chunk number) of every chunk of every long segment
+    float* partials;      // one row of dim floats per chunk
+    uint32_t max_long, max_chunks;
     uint32_t nb;
     size_t bytes;
 };
 
 size_t align_up(size_t x) { return (x + 255) / 256 * 256; }
 
-Workspace carve(void* base, uint64_t n) {
+// dim == 0: the part sort_segment and plan_read use (its offsets do not depend on dim)
+Workspace carve(void* base, uint64_t n, int dim) {
     Workspace w{};
     char* p = (char*)base;
     size_t off = 0;
@@ -115,6 +122,13 @@ Workspace carve(void* base, uint64_t n) {
     w.seg = (uint32_t*)take((n + 1) * 4);
     w.unique = (uint32_t*)take(n * 4);
     w.seg_off = (uint32_t*)take((n + 1) * 4);
+    // a long segment has > SEG_CHUNK entries: at most n/257 of them, fewer than n/128 + 1 chunks in all
+    w.max_long = (uint32_t)(n / (SEG_CHUNK + 1) + 1);
+    w.max_chunks = (uint32_t)(n / (SEG_CHUNK / 2) + 2);
+    w.long_u = (uint32_t*)take((size_t)w.max_long * 4);
+    w.long_base = (uint32_t*)take((size_t)w.max_long * 4);
+    w.chunks = (uint2*)take((size_t)w.max_chunks * 8);
+    w.partials = (float*)take((size_t)w.max_chunks * (size_t)dim * 4);
     w.bytes = off;
     return w;
 }
@@ -362,48 +376,145 @@ __device__ __forceinline__ float upd1(float g_sum, float row, float& acc, float 
     return __fsub_rn(row, __fdiv_rn(__fmul_rn(lr, g), __fsqrt_rn(acc)));
 }
 
+struct ApplyArgs {
+    const uint32_t* hdr_ro;
+    uint32_t* hdr;
+    const uint32_t* perm;
+    const uint32_t* unique;
+    const uint32_t* seg_off;
+    uint32_t* long_u;
+    uint32_t* long_base;
+    uint2* chunks;
+    float* partials;
+    float inv_w, lr;
+};
+
+// left fold of column c over sorted entries [j0, j1) of the plan, eight gradient rows in flight
+__device__ __forceinline__ float4 fold_rows(const RowSources& gs, const uint32_t* __restrict__ perm, uint32_t j0, uint32_t j1,
+                                            int dim, int c) {
+    float4 acc = ldg_row4(grad_row(gs, perm[j0], dim), c);
+    uint32_t j = j0 + 1;
+    for (; j + 8 <= j1; j += 8) {
+        float4 r[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) r[k] = ldg_row4(grad_row(gs, perm[j + k], dim), c);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc = add4(acc, r[k]);
+    }
+    for (; j < j1; ++j) acc = add4(acc, ldg_row4(grad_row(gs, perm[j], dim), c));
+    return acc;
+}
+
+template <bool ADAGRAD>
+__device__ __forceinline__ void update_row(float* row, float* arow, int c, const float4& total, float inv_w, float lr) {
+    float4 r = reinterpret_cast<float4*>(row)[c];
+    float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ADAGRAD) ac = reinterpret_cast<float4*>(arow)[c];
+    r.x = upd1<ADAGRAD>(total.x, r.x, ac.x, inv_w, lr);
+    r.y = upd1<ADAGRAD>(total.y, r.y, ac.y, inv_w, lr);
+    r.z = upd1<ADAGRAD>(total.z, r.z, ac.z, inv_w, lr);
+    r.w = upd1<ADAGRAD>(total.w, r.w, ac.w, inv_w, lr);
+    reinterpret_cast<float4*>(row)[c] = r;
+    if (ADAGRAD) reinterpret_cast<float4*>(arow)[c] = ac;
+}
+
+// Segments of at most SEG_CHUNK entries: fold and update here.  Longer ones (hot ids) are only
+// registered -- their chunks are folded by all lane groups of long_partials_kernel and finished by
+// long_final_kernel, in the chunk order the oracle defines.
 template <int LG, bool ADAGRAD>
 __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant__ ShardBases tb,
                                                            const __grid_constant__ RowSources gs,
-                                                           const __grid_constant__ Geom g, const uint32_t* __restrict__ hdr,
-                                                           const uint32_t* __restrict__ perm,
-                                                           const uint32_t* __restrict__ unique,
-                                                           const uint32_t* __restrict__ seg_off, float inv_w, float lr) {
-    const uint32_t n_unique = hdr[HDR_UNIQUE];
+                                                           const __grid_constant__ Geom g,
+                                                           const __grid_constant__ ApplyArgs a) {
+    const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
     const int lane = threadIdx.x % LG;
     const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
     const int dim4 = g.dim / 4;
-    for (uint32_t u = group; u < n_unique; u += ngroups) {
+    // the metadata of the next unique id is fetched while the rows of this one are in flight
+    uint32_t u = group;
+    uint32_t s0 = 0, s1 = 0, id = 0, first = 0;
+    if (u < n_unique) {
+        s0 = a.seg_off[u];
+        s1 = a.seg_off[u + 1];
+        id = a.unique[u];
+        first = a.perm[s0];
+    }
+    while (u < n_unique) {
+        const uint32_t un = u + ngroups;
+        uint32_t n0 = 0, n1 = 0, nid = 0, nfirst = 0;
+        if (un < n_unique) {
+            n0 = a.seg_off[un];
+            n1 = a.seg_off[un + 1];
+            nid = a.unique[un];
+            nfirst = a.perm[n0];
+        }
+        const uint32_t len = s1 - s0;
+        if (len > SEG_CHUNK) {
+            const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK;
+            uint32_t base = 0;
+            if (lane == 0) {
+                const uint32_t idx = atomicAdd(&a.hdr[HDR_NLONG], 1u);
+                base = atomicAdd(&a.hdr[HDR_NCHUNKS], nchunks);
+                a.long_u[idx] = u;
+                a.long_base[idx] = base;
+            }
+            const int g0 = (threadIdx.x & 31) / LG * LG;  // first lane of this group inside the warp
+            base = __shfl_sync(LG == 32 ? 0xffffffffu : (((1u << LG) - 1u) << g0), base, g0);
+            for (uint32_t j = lane; j < nchunks; j += LG) a.chunks[base + j] = make_uint2(u, j);
+        } else {
+            uint64_t lrow;
+            const int s = owner_of(g, id, &lrow);
+            float* row = tb.base[s] + lrow * (uint64_t)g.dim;
+            float* arow = ADAGRAD ? tb.accum[s] + lrow * (uint64_t)g.dim : nullptr;
+            for (int c = lane; c < dim4; c += LG) {
+                float4 acc = ldg_row4(grad_row(gs, first, g.dim), c);
+                if (len > 1) acc = add4(acc, fold_rows(gs, a.perm, s0 + 1, s1, g.dim, c));
+                update_row<ADAGRAD>(row, arow, c, acc, a.inv_w, a.lr);
+            }
+        }
+        u = un;
+        s0 = n0;
+        s1 = n1;
+        id = nid;
+        first = nfirst;
+    }
+}
+
+template <int LG>
+__global__ void __launch_bounds__(256) long_partials_kernel(const __grid_constant__ RowSources gs, const __grid_constant__ Geom g,
+                                                            const __grid_constant__ ApplyArgs a) {
+    const uint32_t nchunks = a.hdr_ro[HDR_NCHUNKS];
+    const int lane = threadIdx.x % LG;
+    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint32_t ci = group; ci < nchunks; ci += ngroups) {
+        const uint2 d = a.chunks[ci];
+        const uint32_t s0 = a.seg_off[d.x], s1 = a.seg_off[d.x + 1];
+        const uint32_t j0 = s0 + d.y * SEG_CHUNK, j1 = s1 - j0 < SEG_CHUNK ? s1 : j0 + SEG_CHUNK;
+        for (int c = lane; c < dim4; c += LG)
+            reinterpret_cast<float4*>(a.partials + (uint64_t)ci * (uint64_t)g.dim)[c] = fold_rows(gs, a.perm, j0, j1, g.dim, c);
+    }
+}
+
+template <int LG, bool ADAGRAD>
+__global__ void __launch_bounds__(256) long_final_kernel(const __grid_constant__ ShardBases tb, const __grid_constant__ Geom g,
+                                                         const __grid_constant__ ApplyArgs a) {
+    const uint32_t nlong = a.hdr_ro[HDR_NLONG];
+    const int lane = threadIdx.x % LG;
+    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint32_t li = group; li < nlong; li += ngroups) {
+        const uint32_t u = a.long_u[li], base = a.long_base[li];
+        const uint32_t len = a.seg_off[u + 1] - a.seg_off[u], nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK;
         uint64_t lrow;
-        const int s = owner_of(g, unique[u], &lrow);
+        const int s = owner_of(g, a.unique[u], &lrow);
         float* row = tb.base[s] + lrow * (uint64_t)g.dim;
         float* arow = ADAGRAD ? tb.accum[s] + lrow * (uint64_t)g.dim : nullptr;
-        const uint32_t a = seg_off[u], b = seg_off[u + 1];
         for (int c = lane; c < dim4; c += LG) {
-            float4 total = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (uint32_t c0 = a; c0 < b; c0 += SEG_CHUNK) {
-                const uint32_t c1 = b - c0 < SEG_CHUNK ? b : c0 + SEG_CHUNK;
-                float4 acc = ldg_row4(grad_row(gs, perm[c0], g.dim), c);
-                uint32_t j = c0 + 1;
-                for (; j + 4 <= c1; j += 4) {  // four rows in flight, added in order
-                    const float4 r0 = ldg_row4(grad_row(gs, perm[j], g.dim), c);
-                    const float4 r1 = ldg_row4(grad_row(gs, perm[j + 1], g.dim), c);
-                    const float4 r2 = ldg_row4(grad_row(gs, perm[j + 2], g.dim), c);
-                    const float4 r3 = ldg_row4(grad_row(gs, perm[j + 3], g.dim), c);
-                    acc = add4(add4(add4(add4(acc, r0), r1), r2), r3);
-                }
-                for (; j < c1; ++j) acc = add4(acc, ldg_row4(grad_row(gs, perm[j], g.dim), c));
-                total = c0 == a ? acc : add4(total, acc);
-            }
-            float4 r = reinterpret_cast<float4*>(row)[c];
-            float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ADAGRAD) ac = reinterpret_cast<float4*>(arow)[c];
-            r.x = upd1<ADAGRAD>(total.x, r.x, ac.x, inv_w, lr);
-            r.y = upd1<ADAGRAD>(total.y, r.y, ac.y, inv_w, lr);
-            r.z = upd1<ADAGRAD>(total.z, r.z, ac.z, inv_w, lr);
-            r.w = upd1<ADAGRAD>(total.w, r.w, ac.w, inv_w, lr);
-            reinterpret_cast<float4*>(row)[c] = r;
-            if (ADAGRAD) reinterpret_cast<float4*>(arow)[c] = ac;
+            const float4* p = reinterpret_cast<const float4*>(a.partials + (uint64_t)base * (uint64_t)g.dim) + c;
+            float4 total = p[0];
+            for (uint32_t j = 1; j < nchunks; ++j) total = add4(total, p[(uint64_t)j * (uint64_t)dim4]);
+            update_row<ADAGRAD>(row, arow, c, total, a.inv_w, a.lr);
         }
     }
 }
@@ -415,20 +526,35 @@ template <int LG>
 __global__ void __launch_bounds__(256) sparse_gather_kernel(float* __restrict__ out, const __grid_constant__ ShardBases tb,
                                                             const __grid_constant__ Geom g, const int64_t* __restrict__ ids,
                                                             uint64_t n) {
+    constexpr int R = 4;  // rows in flight per lane group
     const int lane = threadIdx.x % LG;
     const uint64_t group = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = (uint64_t)gridDim.x * blockDim.x / LG;
     const int dim4 = g.dim / 4;
-    for (uint64_t k = group; k < n; k += ngroups) {
-        const int64_t id = ids[k];
-        float4* dst = reinterpret_cast<float4*>(out + k * (uint64_t)g.dim);
-        if (id < 0 || (uint64_t)id >= g.rows) {  // out-of-range id: a row of zeros
-            for (int c = lane; c < dim4; c += LG) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-            continue;
+    for (uint64_t k0 = group; k0 < n; k0 += R * ngroups) {
+        const float4* src[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint64_t k = k0 + (uint64_t)r * ngroups;
+            src[r] = nullptr;
+            if (k < n) {
+                const int64_t id = ids[k];
+                if (id >= 0 && (uint64_t)id < g.rows) {
+                    uint64_t lrow;
+                    const int s = owner_of(g, (uint64_t)id, &lrow);
+                    src[r] = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
+                }
+            }
         }
-        uint64_t lrow;
-        const int s = owner_of(g, (uint64_t)id, &lrow);
-        const float4* src = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
-        for (int c = lane; c < dim4; c += LG) dst[c] = src[c];
+        for (int c = lane; c < dim4; c += LG) {
+            float4 v[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) v[r] = src[r] ? src[r][c] : make_float4(0.f, 0.f, 0.f, 0.f);  // bad id: zero row
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint64_t k = k0 + (uint64_t)r * ngroups;
+                if (k < n) reinterpret_cast<float4*>(out + k * (uint64_t)g.dim)[c] = v[r];
+            }
+        }
     }
 }
 
@@ -500,18 +626,32 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
                        "gradient rows of worker %d must be a 16-byte aligned device pointer", w);
         gs.rows[w] = d_grad_rows[w];
     }
-    const Workspace ws = carve(const_cast<void*>(d_workspace), n);
+    const Workspace ws = carve(const_cast<void*>(d_workspace), n, g.dim);
     const int passes = key_passes(g.rows);
-    const uint32_t* perm = ws.val[passes & 1];  // the partition wrote buffer 0, each radix pass flips
+    ApplyArgs a{};
+    a.hdr_ro = ws.hdr;
+    a.hdr = ws.hdr;
+    a.perm = ws.val[passes & 1];  // the partition wrote buffer 0, each radix pass flips
+    a.unique = ws.unique;
+    a.seg_off = ws.seg_off;
+    a.long_u = ws.long_u;
+    a.long_base = ws.long_base;
+    a.chunks = ws.chunks;
+    a.partials = ws.partials;
+    a.inv_w = 1.0f / (float)W;
+    a.lr = lr;
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     const int lg = lane_group(g.dim);
-    const float inv_w = 1.0f / (float)W;
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH_APPLY(LG) \
-    sparse_apply_kernel<LG, ADAGRAD><<<grid, 256, 0, st>>>(tb, gs, g, ws.hdr, perm, ws.unique, ws.seg_off, inv_w, lr)
+    // the long-segment counters belong to this apply (a plan may be applied more than once)
+    B200PS_CUDA(cudaMemsetAsync(ws.hdr + HDR_NLONG, 0, 2 * sizeof(uint32_t), st));
+#define LAUNCH_APPLY(LG)                                                      \
+    sparse_apply_kernel<LG, ADAGRAD><<<grid, 256, 0, st>>>(tb, gs, g, a);     \
+    long_partials_kernel<LG><<<sms * 8, 256, 0, st>>>(gs, g, a);              \
+    long_final_kernel<LG, ADAGRAD><<<sms, 256, 0, st>>>(tb, g, a)
     switch (lg) {
         case 4: LAUNCH_APPLY(4); break;
         case 8: LAUNCH_APPLY(8); break;
@@ -520,7 +660,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     }
 #undef LAUNCH_APPLY
     B200PS_CUDA(cudaGetLastError());
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    g_launches.fetch_add(3, std::memory_order_relaxed);
     return B200PS_OK;
 }
 
@@ -529,7 +669,9 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
 
 using namespace b200ps;
 
-extern "C" size_t b200ps_sparse_workspace_bytes(uint64_t n_total) { return carve(nullptr, n_total ? n_total : 1).bytes; }
+extern "C" size_t b200ps_sparse_workspace_bytes(uint64_t n_total, int dim) {
+    return carve(nullptr, n_total ? n_total : 1, dim > 0 ? dim : 0).bytes;
+}
 
 extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_base, const b200ps_table_geom_t* geom,
                                     const int64_t* d_ids, uint64_t n, void* stream) {
@@ -572,7 +714,7 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     const uint64_t n = (uint64_t)W * ids_per_worker;
     B200PS_REQUIRE(n >= 1 && n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be in 1..2^32-2");
     B200PS_REQUIRE(((uintptr_t)d_workspace & 255) == 0, B200PS_ERR_INVALID, "workspace must be 256-byte aligned");
-    const Workspace ws = carve(d_workspace, n);
+    const Workspace ws = carve(d_workspace, n, g.dim);
     B200PS_REQUIRE(workspace_bytes >= ws.bytes, B200PS_ERR_RANGE, "workspace of %zu bytes is too small: %zu needed",
                    workspace_bytes, ws.bytes);
     IdSources src{};
@@ -643,7 +785,7 @@ extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total
                                        int32_t* h_seg_id, int64_t* h_unique_ids, uint32_t* h_seg_offset, void* stream) {
     B200PS_REQUIRE(d_workspace && n_total >= 1 && rows >= 1, B200PS_ERR_INVALID, "null workspace or empty plan");
     cudaStream_t st = (cudaStream_t)stream;
-    const Workspace ws = carve(const_cast<void*>(d_workspace), n_total);
+    const Workspace ws = carve(const_cast<void*>(d_workspace), n_total, 0);
     uint32_t hdr[HDR_WORDS];
     B200PS_CUDA(cudaMemcpyAsync(hdr, ws.hdr, sizeof hdr, cudaMemcpyDeviceToHost, st));
     B200PS_CUDA(cudaStreamSynchronize(st));
@@ -717,7 +859,8 @@ extern "C" int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const 
                    "push of %llu entries (W * ids_per_worker) exceeds the %llu the static scratch holds; "
                    "use b200ps_sparse_sort_segment + b200ps_sparse_apply_sgd with your own workspace",
                    (unsigned long long)n, (unsigned long long)B200PS_NOALLOC_MAX_ENTRIES);
-    const size_t need = carve(nullptr, n).bytes;
+    B200PS_REQUIRE(geom, B200PS_ERR_INVALID, "null table geometry");
+    const size_t need = carve(nullptr, n, geom->dim > 0 ? geom->dim : 0).bytes;
     B200PS_REQUIRE(need <= (size_t)B200PS_NOALLOC_SCRATCH_BYTES, B200PS_ERR_RANGE,
                    "static scratch of %llu bytes cannot hold the %zu-byte plan of %llu entries",
                    (unsigned long long)B200PS_NOALLOC_SCRATCH_BYTES, need, (unsigned long long)n);

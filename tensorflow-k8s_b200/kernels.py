@@ -92,9 +92,9 @@ def sparse_gather(out: torch.Tensor, shards: Sequence, geom: TableGeom, ids: tor
     return out
 
 
-def sparse_workspace(n_total: int) -> torch.Tensor:
-    """Scratch for one push of n_total = W * ids_per_worker entries."""
-    return torch.empty(int(lib.b200ps_sparse_workspace_bytes(n_total)), dtype=torch.uint8, device="cuda")
+def sparse_workspace(n_total: int, dim: int) -> torch.Tensor:
+    """Scratch for one push of n_total = W * ids_per_worker entries of a dim-wide table."""
+    return torch.empty(int(lib.b200ps_sparse_workspace_bytes(n_total, dim)), dtype=torch.uint8, device="cuda")
 
 
 def sparse_sort_segment(ids: Sequence, ids_per_worker: int, geom: TableGeom, workspace: torch.Tensor) -> None:

@@ -107,7 +107,7 @@ class EmbeddingTable:
         for w in self.local_workers:
             self.ids[w] = torch.as_tensor(_ByteArray(p.value + self.lay.ids_off[w], B * 8, "<i8", (B,)), device=dev)
             self.grad_rows[w] = torch.as_tensor(_ByteArray(p.value + self.lay.grad_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
-        self.workspace = torch.empty(int(lib.b200ps_sparse_workspace_bytes(num_workers * B)), dtype=torch.uint8, device=dev)
+        self.workspace = torch.empty(int(lib.b200ps_sparse_workspace_bytes(num_workers * B, dim)), dtype=torch.uint8, device=dev)
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
         if world > 1:
             self._exchange_handles()

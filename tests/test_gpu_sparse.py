@@ -47,7 +47,7 @@ def test_sort_segment_bit_exact(oracle, rows, S, dim, W, B, kind):
     rng = np.random.default_rng(rows + W + B)
     ids = make_ids(rng, kind, W, B, rows).astype(np.int64)
     dids = [dev(ids[w]) for w in range(W)]
-    ws = K.sparse_workspace(W * B)
+    ws = K.sparse_workspace(W * B, dim)
     geom = K.table_geom(rows, dim, S)
     K.sparse_sort_segment(dids, B, geom, ws)
     plan = K.sparse_plan_read(ws, W * B, rows)
@@ -74,7 +74,7 @@ def test_push_apply_bit_exact_over_steps(oracle, opt, rows, S, dim, W, B, kind):
     accum = np.full((rows, dim), 0.1, np.float32)
     dt, da = dev(table), dev(accum)
     geom = K.table_geom(rows, dim, S)
-    ws = K.sparse_workspace(W * B)
+    ws = K.sparse_workspace(W * B, dim)
     inv_w = np.float32(1.0) / np.float32(W)
     for step in range(3):
         ids = make_ids(rng, kind, W, B, rows).astype(np.int64)
@@ -114,7 +114,7 @@ def test_partition_keeps_only_this_gpus_shards(oracle):
     table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
     dt = dev(table)
     dids, dgr = [dev(ids[w]) for w in range(W)], [dev(grad[w * B:(w + 1) * B]) for w in range(W)]
-    ws = K.sparse_workspace(W * B)
+    ws = K.sparse_workspace(W * B, dim)
     owners = np.array([oracle.row_owner(rows, S, int(i)) for i in ids.reshape(-1)])
     total_kept = 0
     for rank in range(world):
@@ -136,7 +136,7 @@ def test_partition_keeps_only_this_gpus_shards(oracle):
 def test_out_of_range_ids_are_dropped_and_counted(oracle):
     rows, S, dim = 100, 2, 4
     ids = np.array([[5, -1, 100, 7, 5, 1 << 40]], np.int64)
-    ws = K.sparse_workspace(ids.size)
+    ws = K.sparse_workspace(ids.size, dim)
     K.sparse_sort_segment([dev(ids[0])], ids.shape[1], K.table_geom(rows, dim, S), ws)
     plan = K.sparse_plan_read(ws, ids.size, rows)
     assert plan["n_bad"] == 3 and plan["sorted_ids"].tolist() == [5, 5, 7] and plan["perm"].tolist() == [0, 4, 3]
@@ -147,7 +147,7 @@ def test_out_of_range_ids_are_dropped_and_counted(oracle):
 
 
 def test_argument_errors():
-    ws = K.sparse_workspace(8)
+    ws = K.sparse_workspace(8, 4)
     ids = torch.zeros(8, dtype=torch.int64, device="cuda")
     with pytest.raises(b200ps.B200PSError):
         K.sparse_sort_segment([ids], 8, K.table_geom(100, 6, 1), ws)  # dim not a multiple of 4
@@ -169,7 +169,7 @@ def test_c2_shapes_full_batch(oracle):
     ids = np.minimum(rng.zipf(1.05, (W, B)) - 1, rows - 1).astype(np.int64)
     dids = [dev(ids[w]) for w in range(W)]
     geom = K.table_geom(rows, dim, S)
-    ws = K.sparse_workspace(W * B)
+    ws = K.sparse_workspace(W * B, dim)
     K.sparse_sort_segment(dids, B, geom, ws)
     plan = K.sparse_plan_read(ws, W * B, rows)
     s = plan["sorted_ids"]

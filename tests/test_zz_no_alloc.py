@@ -34,7 +34,7 @@ def test_noalloc_push_matches_workspace_push_twice_in_a_row(rows, S, dim, W, B, 
     geom = K.table_geom(rows, dim, S)
     ref = K.fill_uniform(torch.empty(rows * dim, dtype=torch.float32, device="cuda"), 1, 0, 0).view(rows, dim)
     got = ref.clone()
-    ws = K.sparse_workspace(W * B)
+    ws = K.sparse_workspace(W * B, dim)
     for call in (1, 2):  # the second call reuses the scratch left by the first
         ids, grads = _push_inputs(rng, rows, dim, W, B, call, zipf)
         K.sparse_sort_segment(ids, B, geom, ws)
