@@ -11,9 +11,9 @@
 // kernels of one GPU read all workers' ids and gradient rows wherever they live.
 //
 // push on one GPU, all device-side (no host round trip; counts stay in the workspace header):
-//   1. stable partition of the W*B (worker, position)-ordered ids: keep those of this GPU's shards
-//   2. stable LSD radix sort of the kept ids, 8 bits per pass, ceil(log2(rows)/8) passes,
-//      payload = source entry index -> order (id, worker, position)
+//   1. + 2. stable LSD radix sort of the (worker, position)-ordered ids, 8 bits per pass,
+//      ceil(log2(rows)/8) passes, payload = source entry index -> order (id, worker, position);
+//      the first pass reads the workers' ids and keeps only those of this GPU's shards
 //   3. heads + scan -> segment ids, unique ids, segment offsets
 //   4. one lane group per unique id folds its gradient rows in that fixed order (chunks of 256,
 //      see oracle/ps_oracle.c segment_sum), scales by 1/W and updates the row (SGD / Adagrad)
@@ -216,7 +216,8 @@ cudaError_t scan_exclusive(const uint32_t* in, uint32_t* out, uint32_t n, uint32
 }
 
 // ------------------------------------------------------------------------------------------------
-// stable partition (MODE 0) and stable radix pass (MODE 1)
+// stable radix passes.  MODE 0 = the first pass: reads the workers' ids directly, keeps only the
+// entries of this GPU's shards (a stable partition fused into the pass).  MODE 1 = later passes.
 // ------------------------------------------------------------------------------------------------
 struct PassArgs {
     const uint32_t* key_in;
@@ -224,13 +225,15 @@ struct PassArgs {
     uint32_t* key_out;
     uint32_t* val_out;
     uint32_t* hist;  // BINS x nb, bin-major
+    const uint32_t* total;  // grand total of the scanned histogram (scan_sums[nblk])
     uint32_t* hdr;
     uint32_t nb;
     int shift;
 };
 
-// One entry of the tile.  MODE 0 reads the workers' int64 ids and classifies keep (bin 0) / drop
-// (bin 1); MODE 1 reads the previous pass and takes 8 key bits.  Returns the bin or NONE.
+// One entry of the tile.  MODE 0 reads the workers' int64 ids, drops (NONE) those that are out of
+// range or belong to another GPU's shards, and takes the lowest 8 key bits; MODE 1 reads the
+// previous pass and takes 8 key bits at `shift`.  Returns the bin or NONE.
 template <int MODE>
 __device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSources& src, const Geom& g, uint32_t idx,
                                                uint32_t limit, uint32_t* key, uint32_t* val, bool count_bad) {
@@ -241,11 +244,11 @@ __device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSource
         *val = idx;
         if (id < 0 || (uint64_t)id >= g.rows) {
             if (count_bad) atomicAdd(&a.hdr[HDR_BAD], 1u);
-            return 1;
+            return NONE;
         }
         *key = (uint32_t)id;
         uint64_t lr;
-        return (owner_of(g, (uint64_t)id, &lr) % g.world) == g.rank ? 0u : 1u;
+        return (owner_of(g, (uint64_t)id, &lr) % g.world) == g.rank ? (*key & 255u) : NONE;
     }
     *key = a.key_in[idx];
     *val = a.val_in[idx];
@@ -310,12 +313,12 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
     __syncthreads();
 #pragma unroll
     for (int b = 0; b < ITEMS; ++b) {
-        if (bin[b] == NONE || (MODE == 0 && bin[b] != 0)) continue;
+        if (bin[b] == NONE) continue;
         const uint32_t dst = cnt[w][bin[b]] + rank[b];
         a.key_out[dst] = key[b];
         a.val_out[dst] = val[b];
     }
-    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = a.hist[1 * a.nb + 0];  // base of bin 1 = #kept
+    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = *a.total;  // sum of the histogram = #kept
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -389,11 +392,11 @@ struct ApplyArgs {
     float inv_w, lr;
 };
 
-// left fold of column c over sorted entries [j0, j1) of the plan, eight gradient rows in flight
-__device__ __forceinline__ float4 fold_rows(const RowSources& gs, const uint32_t* __restrict__ perm, uint32_t j0, uint32_t j1,
-                                            int dim, int c) {
-    float4 acc = ldg_row4(grad_row(gs, perm[j0], dim), c);
-    uint32_t j = j0 + 1;
+// continues the left fold of column c: acc + row[j0] + row[j0+1] + ... (sorted entries [j0, j1) of
+// the plan), eight gradient rows in flight, added strictly in order
+__device__ __forceinline__ float4 fold_rows(float4 acc, const RowSources& gs, const uint32_t* __restrict__ perm, uint32_t j0,
+                                            uint32_t j1, int dim, int c) {
+    uint32_t j = j0;
     for (; j + 8 <= j1; j += 8) {
         float4 r[8];
 #pragma unroll
@@ -468,7 +471,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
             float* arow = ADAGRAD ? tb.accum[s] + lrow * (uint64_t)g.dim : nullptr;
             for (int c = lane; c < dim4; c += LG) {
                 float4 acc = ldg_row4(grad_row(gs, first, g.dim), c);
-                if (len > 1) acc = add4(acc, fold_rows(gs, a.perm, s0 + 1, s1, g.dim, c));
+                acc = fold_rows(acc, gs, a.perm, s0 + 1, s1, g.dim, c);
                 update_row<ADAGRAD>(row, arow, c, acc, a.inv_w, a.lr);
             }
         }
@@ -492,7 +495,8 @@ __global__ void __launch_bounds__(256) long_partials_kernel(const __grid_constan
         const uint32_t s0 = a.seg_off[d.x], s1 = a.seg_off[d.x + 1];
         const uint32_t j0 = s0 + d.y * SEG_CHUNK, j1 = s1 - j0 < SEG_CHUNK ? s1 : j0 + SEG_CHUNK;
         for (int c = lane; c < dim4; c += LG)
-            reinterpret_cast<float4*>(a.partials + (uint64_t)ci * (uint64_t)g.dim)[c] = fold_rows(gs, a.perm, j0, j1, g.dim, c);
+            reinterpret_cast<float4*>(a.partials + (uint64_t)ci * (uint64_t)g.dim)[c] =
+                fold_rows(ldg_row4(grad_row(gs, a.perm[j0], g.dim), c), gs, a.perm, j0 + 1, j1, g.dim, c);
     }
 }
 
@@ -631,7 +635,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     ApplyArgs a{};
     a.hdr_ro = ws.hdr;
     a.hdr = ws.hdr;
-    a.perm = ws.val[passes & 1];  // the partition wrote buffer 0, each radix pass flips
+    a.perm = ws.val[(passes - 1) & 1];  // the first pass wrote buffer 0, each later pass flips
     a.unique = ws.unique;
     a.seg_off = ws.seg_off;
     a.long_u = ws.long_u;
@@ -732,26 +736,24 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     a.hist = ws.hist;
     a.hdr = ws.hdr;
     a.nb = ws.nb;
-    // 1. stable partition: kept ids -> key[0], their source entry -> val[0]
-    a.key_out = ws.key[0];
-    a.val_out = ws.val[0];
-    pass_hist_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-    B200PS_CUDA(scan_exclusive(ws.hist, ws.hist, BINS * ws.nb, ws.scan_sums, st, &launches));
-    pass_scatter_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-    launches += 2;
-    // 2. LSD radix passes, ping-pong between the two buffers
+    a.total = ws.scan_sums + (BINS * ws.nb + SCAN_TILE - 1) / SCAN_TILE;
+    // 1 + 2. LSD radix passes, ping-pong between the two buffers; the first one reads the workers'
+    // ids and keeps this GPU's entries (key = id, value = source entry w*B + pos)
     const int passes = key_passes(g.rows);
     int cur = 0;
-    for (int p = 0; p < passes; ++p, cur ^= 1) {
+    for (int p = 0; p < passes; ++p) {
         a.key_in = ws.key[cur];
         a.val_in = ws.val[cur];
-        a.key_out = ws.key[cur ^ 1];
-        a.val_out = ws.val[cur ^ 1];
+        a.key_out = ws.key[p == 0 ? 0 : cur ^ 1];
+        a.val_out = ws.val[p == 0 ? 0 : cur ^ 1];
         a.shift = 8 * p;
-        pass_hist_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        if (p == 0) pass_hist_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        else pass_hist_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
         B200PS_CUDA(scan_exclusive(ws.hist, ws.hist, BINS * ws.nb, ws.scan_sums, st, &launches));
-        pass_scatter_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        if (p == 0) pass_scatter_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        else pass_scatter_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
         launches += 2;
+        if (p > 0) cur ^= 1;
     }
     // 3. segments
     int sms = 0;
@@ -793,7 +795,7 @@ extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total
     if (n_kept) *n_kept = kept;
     if (n_unique) *n_unique = uniq;
     if (n_bad) *n_bad = hdr[HDR_BAD];
-    const int fin = (key_passes(rows)) & 1;  // partition wrote buffer 0, each pass flips
+    const int fin = (key_passes(rows) - 1) & 1;  // the first pass wrote buffer 0, each later pass flips
     std::vector<uint32_t> tmp(kept > uniq + 1 ? kept : uniq + 1);
     if (h_sorted_ids && kept) {
         B200PS_CUDA(cudaMemcpyAsync(tmp.data(), ws.key[fin], kept * 4ull, cudaMemcpyDeviceToHost, st));
