@@ -19,9 +19,9 @@ def _port():
         return s.getsockname()[1]
 
 
-def _run(n, S, W, opt, transport):
+def _run(n, *args, script="_mr_worker.py"):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
-           "--master-port", str(_port()), os.path.join(HERE, "_mr_worker.py"), str(S), str(W), opt, transport]
+           "--master-port", str(_port()), os.path.join(HERE, script)] + [str(a) for a in args]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "MULTIRANK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
@@ -46,3 +46,13 @@ def test_nccl_transport_matches_within_tolerance():
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
     _run(2, 2, 2, "adam", "nccl")
+
+
+@pytest.mark.parametrize("opt,kind", [("sgd", "zipf"), ("adagrad", "uniform")])
+def test_sparse_pull_and_push_across_gpus(opt, kind):
+    """Gather from peer shards; every GPU sorts its shards' ids out of all workers' buffers and folds
+    gradient rows from peer memory: bit-exact against the oracle after 3 steps."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, opt, kind, script="_mr_sparse_worker.py")
