@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--ids", default="zipf", choices=["zipf", "uniform"], help="id distribution of --workload c2")
     ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
+                    help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -376,8 +378,11 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    if os.environ.get("B200PS_DENSE_TUNING"):  # "threads,ctas_per_sm,unroll" -- for geometry experiments
+        K.set_dense_tuning(*[int(x) for x in os.environ["B200PS_DENSE_TUNING"].split(",")])
     label, sizes, S, W, opt = workload(args.workload, world)
-    ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport)
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
+                                aggregate=args.aggregate)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
@@ -478,6 +483,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": ps.plan.P,
                        "transport": args.transport if world > 1 else "local",
+                       "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
                        "l2": "inputs exceed L2 (per step each GPU streams "
                              f"{ps.algorithmic_bytes_per_step() / 1e9:.2f} GB >> 126 MB), no flush needed"},
             "ps_steps_per_sec": round(steps_per_s, 3),

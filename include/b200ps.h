@@ -107,7 +107,7 @@ int b200ps_row_owner(uint64_t rows, int nshards, uint64_t id); /* owner shard or
  * k8s-operator.md:6.  SURVEY.md 8(a) rows a5..a9.
  *
  * One launch is push + aggregate + apply + pull for one PS slice of n elements:
- *   g[i]  = inv_w * (((g_0[i] + g_1[i]) + g_2[i]) + ...)         fixed worker order, W buffers
+ *   g[i]  = inv_w * (((g_0[i] + g_1[i]) + g_2[i]) + ...)         fixed buffer order, W buffers
  *   SGD:    p[i] -= lr * g[i]
  *   Adam:   m = b1*m + omb1*g; v = b2*v + omb2*g*g; p -= (lr_t*m) / (sqrt(v) + eps)
  * then the new p[i] is also written to every d_mirrors[k][i] (the workers' copies on other
@@ -126,11 +126,18 @@ typedef struct {
 int b200ps_adam_scalars(double lr, double beta1, double beta2, double eps, uint64_t t,
                         b200ps_adam_t* out);
 
+/* inv_w is the fp32 constant the folded sum is multiplied by: 1/W for the plain mean over W
+ * workers; 1/(total workers) when the W buffers are themselves per-GPU partial sums (below). */
 int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, uint64_t n,
-                           float lr, float* const* d_mirrors, int n_mirrors, void* stream);
+                           float inv_w, float lr, float* const* d_mirrors, int n_mirrors,
+                           void* stream);
 int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float* const* d_grads,
-                            int W, uint64_t n, const b200ps_adam_t* opt, float* const* d_mirrors,
-                            int n_mirrors, void* stream);
+                            int W, uint64_t n, float inv_w, const b200ps_adam_t* opt,
+                            float* const* d_mirrors, int n_mirrors, void* stream);
+/* d_out[i] = ((b_0[i] + b_1[i]) + b_2[i]) + ...  -- the local half of the two-level aggregation:
+ * a GPU that hosts several workers folds their gradients once (in worker order), and only that
+ * partial sum crosses NVLink; the owning shard then folds the G partials in GPU order. */
+int b200ps_dense_fold(float* d_out, const float* const* d_bufs, int W, uint64_t n, void* stream);
 /* synthetic inputs: d_dst[i] = uniform[-1,1) from the integer hash of (seed, step, worker,
  * first+i); identical to ps_fill_uniform of the oracle */
 int b200ps_fill_uniform(float* d_dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,

@@ -46,6 +46,7 @@ def lib():
         L.ps_row_owner.restype = i32
         L.ps_row_owner.argtypes = [u64, i32, u64]
         L.ps_dense_sgd.argtypes = [vp, vp, i32, u64, f32, f32, i32]
+        L.ps_dense_fold.argtypes = [vp, vp, i32, u64, i32]
         L.ps_adam_scalars.restype = AdamT
         L.ps_adam_scalars.argtypes = [C.c_double] * 4 + [u64]
         L.ps_dense_adam.argtypes = [vp, vp, vp, vp, i32, u64, f32, C.POINTER(AdamT), i32]
@@ -99,10 +100,22 @@ def _gradptrs(grads):
     return arr
 
 
-def dense_sgd(p, grads, lr, threads=1):
+def dense_fold(bufs, threads=1):
+    out = np.empty_like(bufs[0])
+    gp = _gradptrs(bufs)
+    lib().ps_dense_fold(_p(out), C.addressof(gp), len(bufs), out.size, threads)
+    return out
+
+
+def two_level_partials(grads, world, threads=1):
+    """Per-GPU partial sums for the placement worker w -> GPU w mod world (GPUs without workers are skipped)."""
+    return [dense_fold(grads[k::world], threads) for k in range(world) if grads[k::world]]
+
+
+def dense_sgd(p, grads, lr, threads=1, inv_w=None):
     """In place on p (np.float32)."""
     gp = _gradptrs(grads)
-    inv_w = np.float32(1.0) / np.float32(len(grads))
+    inv_w = np.float32(1.0) / np.float32(len(grads)) if inv_w is None else np.float32(inv_w)
     lib().ps_dense_sgd(_p(p), C.addressof(gp), len(grads), p.size, inv_w, lr, threads)
     return p
 
@@ -111,9 +124,9 @@ def adam_scalars(lr, beta1, beta2, eps, t) -> AdamT:
     return lib().ps_adam_scalars(lr, beta1, beta2, eps, t)
 
 
-def dense_adam(p, m, v, grads, a: AdamT, threads=1):
+def dense_adam(p, m, v, grads, a: AdamT, threads=1, inv_w=None):
     gp = _gradptrs(grads)
-    inv_w = np.float32(1.0) / np.float32(len(grads))
+    inv_w = np.float32(1.0) / np.float32(len(grads)) if inv_w is None else np.float32(inv_w)
     lib().ps_dense_adam(_p(p), _p(m), _p(v), C.addressof(gp), len(grads), p.size, inv_w, C.byref(a), threads)
     return p, m, v
 

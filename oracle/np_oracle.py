@@ -68,8 +68,13 @@ def aggregate(grads, inv_w) -> np.ndarray:
     return acc * np.float32(inv_w)
 
 
-def dense_sgd(p, grads, lr):
-    g = aggregate(grads, np.float32(1.0) / np.float32(len(grads)))
+def fold(bufs) -> np.ndarray:
+    """((b0 + b1) + b2) + ... without scaling (the per-GPU partial of the two-level aggregation)."""
+    return aggregate(bufs, np.float32(1.0))
+
+
+def dense_sgd(p, grads, lr, inv_w=None):
+    g = aggregate(grads, np.float32(1.0) / np.float32(len(grads)) if inv_w is None else inv_w)
     return p - np.float32(lr) * g
 
 
@@ -79,8 +84,8 @@ def adam_scalars(lr: float, beta1: float, beta2: float, eps: float, t: int):
                 omb1=np.float32(1.0 - beta1), omb2=np.float32(1.0 - beta2), eps=np.float32(eps))
 
 
-def dense_adam(p, m, v, grads, a):
-    g = aggregate(grads, np.float32(1.0) / np.float32(len(grads)))
+def dense_adam(p, m, v, grads, a, inv_w=None):
+    g = aggregate(grads, np.float32(1.0) / np.float32(len(grads)) if inv_w is None else inv_w)
     m2 = a["beta1"] * m + a["omb1"] * g
     v2 = a["beta2"] * v + a["omb2"] * (g * g)
     p2 = p - (a["lr_t"] * m2) / (np.sqrt(v2) + a["eps"])

@@ -45,6 +45,9 @@ int     ps_row_owner(uint64_t rows, int nshards, uint64_t id);
 /* g = inv_w * (((g0 + g1) + g2) + ...);  p -= lr * g */
 void ps_dense_sgd(float* p, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
                   int threads);
+/* dst = ((b0 + b1) + b2) + ... (two-level aggregation: the per-GPU partial sum; the partials are
+ * then folded in GPU order by ps_dense_* with inv_w = 1 / total workers) */
+void ps_dense_fold(float* dst, const float* const* bufs, int W, uint64_t n, int threads);
 typedef struct {
     float lr_t;   /* lr * sqrt(1 - beta2^t) / (1 - beta1^t), evaluated in double, rounded once */
     float beta1, beta2;

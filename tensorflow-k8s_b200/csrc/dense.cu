@@ -32,7 +32,7 @@ std::atomic<uint64_t> g_launches{0};
 
 namespace {
 
-enum { OPT_SGD = 0, OPT_ADAM = 1 };
+enum { OPT_SGD = 0, OPT_ADAM = 1, OPT_FOLD = 2 };  // FOLD: p[i] = left fold of the buffers, nothing else
 
 struct DenseParams {
     const float* g[B200PS_MAX_WORKERS];
@@ -85,6 +85,10 @@ __device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
 // one element: g = inv_w * sum; optimizer update.  Same operation order as ps_dense_sgd / ps_dense_adam.
 template <int OPT>
 __device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const DenseParams& a) {
+    if (OPT == OPT_FOLD) {
+        p = sum;
+        return;
+    }
     const float g = __fmul_rn(sum, a.inv_w);
     if (OPT == OPT_SGD) {
         p = __fsub_rn(p, __fmul_rn(a.lr, g));
@@ -117,7 +121,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
             for (int u = 0; u < U; ++u) G[w][u] = ld_once(reinterpret_cast<const float4*>(a.g[w]) + i + u * stride, pol);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
+            if (OPT != OPT_FOLD) P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
             if (OPT == OPT_ADAM) {
                 M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
                 V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
@@ -132,7 +136,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
     } else {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
+            if (OPT != OPT_FOLD) P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
             if (OPT == OPT_ADAM) {
                 M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
                 V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
@@ -182,7 +186,7 @@ __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
     for (uint64_t j = a.n4 * 4 + tid; j < a.n; j += stride) {
         float s = a.g[0][j];
         for (int w = 1; w < a.W; ++w) s = __fadd_rn(s, a.g[w][j]);
-        float p = a.p[j], m = 0.f, v = 0.f;
+        float p = OPT == OPT_FOLD ? 0.f : a.p[j], m = 0.f, v = 0.f;
         if (OPT == OPT_ADAM) {
             m = a.m[j];
             v = a.v[j];
@@ -282,7 +286,6 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
         bits |= (uintptr_t)d_mirrors[k];
     }
     a.n4 = (bits & 15) ? 0 : a.n / 4;
-    a.inv_w = 1.0f / (float)a.W;
 
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
@@ -292,8 +295,9 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     const uint64_t cap = (uint64_t)sms * (uint64_t)t.ctas_per_sm;
     const int grid = (int)(want < cap ? (want ? want : 1) : cap);
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = opt == OPT_SGD ? launch_w<OPT_SGD>(a, grid, t.threads, t.unroll, st)
-                                   : launch_w<OPT_ADAM>(a, grid, t.threads, t.unroll, st);
+    cudaError_t e = opt == OPT_SGD    ? launch_w<OPT_SGD>(a, grid, t.threads, t.unroll, st)
+                    : opt == OPT_ADAM ? launch_w<OPT_ADAM>(a, grid, t.threads, t.unroll, st)
+                                      : launch_w<OPT_FOLD>(a, grid, t.threads, t.unroll, st);
     B200PS_CUDA(e);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -317,20 +321,29 @@ extern "C" int b200ps_adam_scalars(double lr, double beta1, double beta2, double
     return B200PS_OK;
 }
 
-extern "C" int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, uint64_t n, float lr,
-                                      float* const* d_mirrors, int n_mirrors, void* stream) {
+extern "C" int b200ps_dense_fold(float* d_out, const float* const* d_bufs, int W, uint64_t n, void* stream) {
+    DenseParams a{};
+    a.p = d_out;
+    a.n = n;
+    a.W = W;
+    return dense_apply(OPT_FOLD, a, d_bufs, nullptr, stream);
+}
+
+extern "C" int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, uint64_t n, float inv_w,
+                                      float lr, float* const* d_mirrors, int n_mirrors, void* stream) {
     DenseParams a{};
     a.p = d_params;
     a.n = n;
     a.W = W;
+    a.inv_w = inv_w;
     a.n_mirror = n_mirrors;
     a.lr = lr;
     return dense_apply(OPT_SGD, a, d_grads, d_mirrors, stream);
 }
 
 extern "C" int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float* const* d_grads, int W,
-                                       uint64_t n, const b200ps_adam_t* opt, float* const* d_mirrors, int n_mirrors,
-                                       void* stream) {
+                                       uint64_t n, float inv_w, const b200ps_adam_t* opt, float* const* d_mirrors,
+                                       int n_mirrors, void* stream) {
     B200PS_REQUIRE(opt, B200PS_ERR_INVALID, "null optimizer scalars");
     DenseParams a{};
     a.p = d_params;
@@ -338,6 +351,7 @@ extern "C" int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, 
     a.v = d_v;
     a.n = n;
     a.W = W;
+    a.inv_w = inv_w;
     a.n_mirror = n_mirrors;
     a.lr = opt->lr_t;
     a.beta1 = opt->beta1;

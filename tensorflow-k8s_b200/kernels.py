@@ -8,6 +8,7 @@ from __future__ import annotations
 import ctypes as C
 from typing import Optional, Sequence
 
+import numpy as np
 import torch
 
 from ._lib import AdamScalars, check, lib
@@ -33,22 +34,39 @@ def adam_scalars(lr: float, beta1: float = 0.9, beta2: float = 0.999, eps: float
     return a
 
 
+def inv_w_f32(total_workers: int) -> float:
+    """The fp32 constant 1/W exactly as the oracle forms it (one fp32 division)."""
+    return float(np.float32(1.0) / np.float32(total_workers))
+
+
 def dense_apply_sgd(params: torch.Tensor, grads: Sequence[torch.Tensor], lr: float,
-                    mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None) -> None:
-    """params -= lr * mean_w(grads[w]) (fixed worker order), then copy params to every mirror."""
+                    mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None, inv_w: Optional[float] = None) -> None:
+    """params -= lr * inv_w * fold(grads) (fixed buffer order), then copy params to every mirror.
+    inv_w defaults to 1/len(grads): the mean over the workers."""
     n = params.numel() if n is None else n
+    inv_w = inv_w_f32(max(len(grads), 1)) if inv_w is None else inv_w
     g = _ptr_array([_dev_f32(t, "grad") for t in grads])
     m = _ptr_array([_dev_f32(t, "mirror") for t in mirrors])
-    check(lib.b200ps_dense_apply_sgd(_dev_f32(params, "params"), g, len(grads), n, lr, m, len(mirrors), _stream()))
+    check(lib.b200ps_dense_apply_sgd(_dev_f32(params, "params"), g, len(grads), n, inv_w, lr, m, len(mirrors), _stream()))
 
 
 def dense_apply_adam(params: torch.Tensor, m: torch.Tensor, v: torch.Tensor, grads: Sequence[torch.Tensor],
-                     opt: AdamScalars, mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None) -> None:
+                     opt: AdamScalars, mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None,
+                     inv_w: Optional[float] = None) -> None:
     n = params.numel() if n is None else n
+    inv_w = inv_w_f32(max(len(grads), 1)) if inv_w is None else inv_w
     g = _ptr_array([_dev_f32(t, "grad") for t in grads])
     mi = _ptr_array([_dev_f32(t, "mirror") for t in mirrors])
     check(lib.b200ps_dense_apply_adam(_dev_f32(params, "params"), _dev_f32(m, "m"), _dev_f32(v, "v"), g, len(grads), n,
-                                      C.byref(opt), mi, len(mirrors), _stream()))
+                                      inv_w, C.byref(opt), mi, len(mirrors), _stream()))
+
+
+def dense_fold(out: torch.Tensor, bufs: Sequence[torch.Tensor], n: Optional[int] = None) -> torch.Tensor:
+    """out = ((b0 + b1) + b2) + ... : the per-GPU partial sum of the two-level aggregation."""
+    n = out.numel() if n is None else n
+    b = _ptr_array([_dev_f32(t, "buffer") for t in bufs])
+    check(lib.b200ps_dense_fold(_dev_f32(out, "out"), b, len(bufs), n, _stream()))
+    return out
 
 
 def fill_uniform(dst: torch.Tensor, seed: int, step: int, worker: int, first: int = 0) -> torch.Tensor:

@@ -41,7 +41,9 @@ class Launch:
     shard: int
     begin: int  # element range of the slice in the flat buffer
     end: int
-    grad_src: List[Tuple[int, int]]  # per worker, in worker order: (rank, arena offset in elements)
+    # buffers the kernel folds, in fold order: (rank, arena offset in elements).  "flat": one per
+    # worker, worker order.  "two_level": one per GPU that hosts workers (its partial sum), GPU order.
+    grad_src: List[Tuple[int, int]]
     mirror_ranks: List[int]  # ranks whose replica receives the updated slice (all but this one)
 
 
@@ -54,28 +56,48 @@ class Plan:
     S: int
     local_workers: List[int]
     local_shards: List[int]
-    arena_elems: int  # replica + one gradient buffer per local worker
+    arena_elems: int  # replica [+ partial sum] + one gradient buffer per local worker
+    aggregate: str = "flat"
     launches: List[Launch] = field(default_factory=list)
+
+    @property
+    def two_level(self) -> bool:
+        """Two-level aggregation only differs from the flat fold when there are several GPUs."""
+        return self.aggregate == "two_level" and self.world > 1
+
+    @property
+    def first_grad_slot(self) -> int:
+        return 2 if self.two_level else 1  # arena slot 0 = replica, slot 1 = partial sum (two-level)
 
     def grad_offset(self, worker: int) -> Tuple[int, int]:
         """(rank, element offset in that rank's arena) of a worker's gradient buffer."""
         r = placement_gpu(worker, self.world)
-        return r, self.P * (1 + worker // self.world)
+        return r, self.P * (self.first_grad_slot + worker // self.world)
 
 
-def build_plan(smap: ShardMap, num_workers: int, rank: int, world: int) -> Plan:
+def build_plan(smap: ShardMap, num_workers: int, rank: int, world: int, aggregate: str = "flat") -> Plan:
+    """aggregate="flat": g = (1/W) * left fold over the workers in worker order.
+    aggregate="two_level": every GPU first folds its own workers (worker order) into one partial
+    sum; the owner of a slice folds the partials in GPU order and scales by 1/W.  Same bits as
+    "flat" on one GPU; on G GPUs only one buffer per GPU crosses NVLink instead of one per worker."""
     S, P = smap.nshards, smap.total
+    if aggregate not in ("flat", "two_level"):
+        raise ValueError("aggregate must be 'flat' or 'two_level'")
     if not (0 <= rank < world):
         raise ValueError(f"rank {rank} is outside 0..{world - 1}")
     if world - 1 > 8:
         raise ValueError("one launch writes at most 8 peer replicas (B200PS_MAX_MIRRORS)")
     lw = [w for w in range(num_workers) if placement_gpu(w, world) == rank]
     ls = [s for s in range(S) if placement_gpu(s, world) == rank]
-    plan = Plan(rank, world, P, num_workers, S, lw, ls, P * (1 + len(lw)))
+    plan = Plan(rank, world, P, num_workers, S, lw, ls, 0, aggregate)
+    plan.arena_elems = P * (plan.first_grad_slot + len(lw))
+    if plan.two_level:
+        src = [(r, P) for r in range(world) if any(placement_gpu(w, world) == r for w in range(num_workers))]
+    else:
+        src = [plan.grad_offset(w) for w in range(num_workers)]
     for s in ls:
         b, e = smap.slice(s)
-        plan.launches.append(Launch(s, b, e, [plan.grad_offset(w) for w in range(num_workers)],
-                                    [r for r in range(world) if r != rank]))
+        plan.launches.append(Launch(s, b, e, list(src), [r for r in range(world) if r != rank]))
     return plan
 
 
@@ -115,7 +137,8 @@ class ParameterServer:
 
     def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
                  lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
-                 world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20):
+                 world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20,
+                 aggregate: str = "flat"):
         if optimizer not in ("sgd", "adam"):
             raise ValueError("optimizer must be 'sgd' or 'adam'")
         if transport not in ("peer", "nccl"):
@@ -123,7 +146,7 @@ class ParameterServer:
         if not torch.cuda.is_available():
             raise RuntimeError("b200ps.ParameterServer needs a CUDA device: there is no CPU fallback")
         self.map = ShardMap(var_numel, num_shards)
-        self.plan = build_plan(self.map, num_workers, rank, world)
+        self.plan = build_plan(self.map, num_workers, rank, world, aggregate)
         self.optimizer, self.lr, self.betas, self.eps = optimizer, lr, (beta1, beta2), eps
         self.rank, self.world, self.group, self.transport = rank, world, group, transport
         self.chunk = max(1024, chunk_elems // 1024 * 1024)
@@ -131,8 +154,11 @@ class ParameterServer:
         P = self.plan.P
         self.arena = Arena(self.plan.arena_elems)
         self.replica = self.arena.tensor[:P]
-        self.grads: Dict[int, torch.Tensor] = {w: self.arena.tensor[P * (1 + i): P * (2 + i)]
+        g0 = self.plan.first_grad_slot
+        self.partial = self.arena.tensor[P: 2 * P] if self.plan.two_level else None
+        self.grads: Dict[int, torch.Tensor] = {w: self.arena.tensor[P * (g0 + i): P * (g0 + i + 1)]
                                                for i, w in enumerate(self.plan.local_workers)}
+        self.inv_w = float(np.float32(1.0) / np.float32(num_workers))
         self.state: Dict[int, Tuple[torch.Tensor, torch.Tensor]] = {}
         if optimizer == "adam":
             for L in self.plan.launches:
@@ -222,13 +248,14 @@ class ParameterServer:
         g = _ptrs([self.peer_base[r] + 4 * (off + lo) for r, off in L.grad_src])
         mir = _ptrs([self.peer_base[r] + 4 * lo for r in L.mirror_ranks])
         p = C.c_void_p(self.arena.ptr + 4 * lo)
+        nbuf = len(L.grad_src)
         if a is None:
-            check(lib.b200ps_dense_apply_sgd(p, g, self.plan.W, n, self.lr, mir, len(L.mirror_ranks), self._stream()))
+            check(lib.b200ps_dense_apply_sgd(p, g, nbuf, n, self.inv_w, self.lr, mir, len(L.mirror_ranks), self._stream()))
         else:
             m, v = self.state[L.shard]
             o = 4 * (lo - L.begin)
-            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr() + o), C.c_void_p(v.data_ptr() + o), g,
-                                              self.plan.W, n, C.byref(a), mir, len(L.mirror_ranks), self._stream()))
+            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr() + o), C.c_void_p(v.data_ptr() + o), g, nbuf, n,
+                                              self.inv_w, C.byref(a), mir, len(L.mirror_ranks), self._stream()))
 
     def step(self):
         """push + aggregate + apply + pull for every local shard; gradients are already in the
@@ -237,7 +264,12 @@ class ParameterServer:
         a = self._opt_scalars()
         if self.transport == "nccl" and self.world > 1:
             return self._step_nccl(a)
-        self._barrier()  # every worker's gradient is in place
+        if self.plan.two_level and self.plan.local_workers:
+            # local half of the aggregation: one partial sum per GPU, before anything crosses NVLink
+            bufs = _ptrs([self.grads[w].data_ptr() for w in self.plan.local_workers])
+            check(lib.b200ps_dense_fold(C.c_void_p(self.partial.data_ptr()), bufs, len(self.plan.local_workers),
+                                        self.plan.P, self._stream()))
+        self._barrier()  # every worker's gradient (or every GPU's partial sum) is in place
         for L in self.plan.launches:
             if L.end > L.begin:
                 self._launch(L, L.begin, L.end, a)
@@ -252,11 +284,11 @@ class ParameterServer:
         dist.reduce_scatter_tensor(self._gsum, g, op=dist.ReduceOp.AVG, group=self.group)
         gp = _ptrs([self._gsum.data_ptr()])
         p = C.c_void_p(self.arena.ptr + 4 * L.begin)
-        if a is None:
-            check(lib.b200ps_dense_apply_sgd(p, gp, 1, n, self.lr, _ptrs([]), 0, self._stream()))
+        if a is None:  # NCCL already averaged: inv_w = 1
+            check(lib.b200ps_dense_apply_sgd(p, gp, 1, n, 1.0, self.lr, _ptrs([]), 0, self._stream()))
         else:
             m, v = self.state[L.shard]
-            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr()), C.c_void_p(v.data_ptr()), gp, 1, n,
+            check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr()), C.c_void_p(v.data_ptr()), gp, 1, n, 1.0,
                                               C.byref(a), _ptrs([]), 0, self._stream()))
         dist.all_gather_into_tensor(self.replica, self.replica[L.begin:L.end], group=self.group)
 
@@ -321,6 +353,8 @@ class ParameterServer:
         return out
 
     def algorithmic_bytes_per_step(self) -> int:
-        """(4W + 8) n for SGD, (4W + 24) n for Adam, summed over local slices."""
+        """(4W + 8) n for SGD, (4W + 24) n for Adam, summed over local slices.
+        (Two-level aggregation moves more local bytes -- the partial sum is written and re-read --
+        but the algorithmic figure is the same: W gradients in, one update out.)"""
         k = 4 * self.plan.W + (24 if self.optimizer == "adam" else 8)
         return sum(k * (L.end - L.begin) for L in self.plan.launches)

@@ -16,12 +16,13 @@ from oracle import c_oracle as O  # noqa: E402
 
 def main():
     S, W, opt, transport, steps = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3], sys.argv[4], 3
+    aggregate = sys.argv[5] if len(sys.argv) > 5 else "flat"
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sizes = [700_000, 333, 123_456, 2_000_000]
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, lr=1e-3 if opt == "adam" else 0.05, rank=rank, world=world,
-                                transport=transport)
+                                transport=transport, aggregate=aggregate)
     ps.init_uniform(1)
     P = ps.plan.P
     hp = O.fill_uniform(P, 1, 0, 0, threads=4)
@@ -31,10 +32,13 @@ def main():
             K.fill_uniform(ps.grad_buffer(w), 2, t, w)
         ps.step()
         hg = [O.fill_uniform(P, 2, t, w, threads=4) for w in range(W)]
+        inv_w = np.float32(1.0) / np.float32(W)
+        if aggregate == "two_level":  # the oracle folds per-GPU partials, then the partials
+            hg = O.two_level_partials(hg, world, threads=4)
         if opt == "adam":
-            O.dense_adam(hp, hm, hv, hg, O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), threads=4)
+            O.dense_adam(hp, hm, hv, hg, O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), threads=4, inv_w=inv_w)
         else:
-            O.dense_sgd(hp, hg, 0.05, threads=4)
+            O.dense_sgd(hp, hg, 0.05, threads=4, inv_w=inv_w)
     torch.cuda.synchronize()
     got = ps.replica.cpu().numpy()
     if transport == "peer":  # fixed worker order: bit-exact on every rank's replica

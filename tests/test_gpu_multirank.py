@@ -56,3 +56,13 @@ def test_sparse_pull_and_push_across_gpus(opt, kind):
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
     _run(2, opt, kind, script="_mr_sparse_worker.py")
+
+
+@pytest.mark.parametrize("S,W,opt", [(4, 8, "adam"), (2, 5, "sgd"), (2, 1, "adam")])
+def test_two_level_aggregation_is_bit_exact(S, W, opt):
+    """Each GPU folds its own workers first, one partial per GPU crosses NVLink; the oracle does
+    the same two-level fold, so every replica still matches bit for bit."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, S, W, opt, "peer", "two_level")

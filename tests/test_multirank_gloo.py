@@ -20,20 +20,23 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, sizes, S, W, opt, steps, out_dir):
+def _worker(rank, world, port, sizes, S, W, opt, steps, out_dir, aggregate="flat"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from oracle import c_oracle as O
 
     smap = b200ps.ShardMap(sizes, S)
-    plan = b200ps.build_plan(smap, W, rank, world)
-    P = plan.P
+    plan = b200ps.build_plan(smap, W, rank, world, aggregate)
+    P, g0 = plan.P, plan.first_grad_slot
+    inv_w = np.float32(1.0) / np.float32(W)
     arena = np.zeros(plan.arena_elems, np.float32)
     arena[:P] = O.fill_uniform(P, 1, 0, 0)                         # replica
     state = {L.shard: (np.zeros(L.end - L.begin, np.float32), np.zeros(L.end - L.begin, np.float32)) for L in plan.launches}
     for t in range(1, steps + 1):
         for i, w in enumerate(plan.local_workers):                 # local workers write their gradients
-            arena[P * (1 + i): P * (2 + i)] = O.fill_uniform(P, 2, t, w)
+            arena[P * (g0 + i): P * (g0 + i + 1)] = O.fill_uniform(P, 2, t, w)
+        if plan.two_level and plan.local_workers:                  # local half of the aggregation
+            arena[P:2 * P] = O.dense_fold([arena[P * (g0 + i): P * (g0 + i + 1)].copy() for i in range(len(plan.local_workers))])
         # "peer memory": every rank can read every arena
         sizes_all = [None] * world
         dist.all_gather_object(sizes_all, arena.size)
@@ -51,9 +54,9 @@ def _worker(rank, world, port, sizes, S, W, opt, steps, out_dir):
             p = arena[L.begin:L.end]
             if opt == "adam":
                 m, v = state[L.shard]
-                O.dense_adam(p, m, v, grads, O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t)) if n else None
+                O.dense_adam(p, m, v, grads, O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), inv_w=inv_w) if n else None
             else:
-                O.dense_sgd(p, grads, 0.05) if n else None
+                O.dense_sgd(p, grads, 0.05, inv_w=inv_w) if n else None
             updated[(L.begin, L.end)] = (p.copy(), L.mirror_ranks)
             assert sorted(L.mirror_ranks + [rank]) == list(range(world))
         allup = [None] * world                                     # mirror stores
@@ -66,19 +69,24 @@ def _worker(rank, world, port, sizes, S, W, opt, steps, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,S,W,opt", [(2, 2, 4, "adam"), (2, 1, 2, "sgd"), (2, 3, 3, "adam"), (4, 2, 4, "sgd")])
-def test_plan_executes_to_the_single_process_result(tmp_path, oracle, world, S, W, opt):
+@pytest.mark.parametrize("world,S,W,opt,aggregate", [(2, 2, 4, "adam", "flat"), (2, 1, 2, "sgd", "flat"), (2, 3, 3, "adam", "flat"),
+                                                     (4, 2, 4, "sgd", "flat"), (2, 2, 8, "adam", "two_level"),
+                                                     (4, 3, 6, "sgd", "two_level")])
+def test_plan_executes_to_the_single_process_result(tmp_path, oracle, world, S, W, opt, aggregate):
     sizes, steps = [5000, 77, 3000], 3
-    mp.spawn(_worker, args=(world, _free_port(), sizes, S, W, opt, steps, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), sizes, S, W, opt, steps, str(tmp_path), aggregate), nprocs=world, join=True)
     P = b200ps.ShardMap(sizes, S).total
     p = oracle.fill_uniform(P, 1, 0, 0)
     m, v = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    inv_w = np.float32(1.0) / np.float32(W)
     for t in range(1, steps + 1):
         g = [oracle.fill_uniform(P, 2, t, w) for w in range(W)]
+        if aggregate == "two_level":
+            g = oracle.two_level_partials(g, world)
         if opt == "adam":
-            oracle.dense_adam(p, m, v, g, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t))
+            oracle.dense_adam(p, m, v, g, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), inv_w=inv_w)
         else:
-            oracle.dense_sgd(p, g, 0.05)
+            oracle.dense_sgd(p, g, 0.05, inv_w=inv_w)
     for r in range(world):
         got = np.load(tmp_path / f"replica{r}.npy")
         assert np.array_equal(got.view(np.uint32), p.view(np.uint32)), f"rank {r} replica differs"
@@ -103,3 +111,10 @@ def test_plan_layout():
     assert [len(p.launches) for p in p4] == [1, 1, 0, 0]
     with pytest.raises(ValueError):
         b200ps.build_plan(smap, 4, 2, 2)
+    # two-level: one partial sum per GPU is folded, arena gains the partial slot
+    t2 = [b200ps.build_plan(smap, 8, r, 2, "two_level") for r in range(2)]
+    assert all(p.arena_elems == (2 + 4) * P for p in t2) and t2[0].launches[0].grad_src == [(0, P), (1, P)]
+    assert t2[1].grad_offset(3) == (1, 3 * P)
+    # on one GPU two-level IS the flat fold
+    one = b200ps.build_plan(smap, 4, 0, 1, "two_level")
+    assert not one.two_level and one.arena_elems == solo.arena_elems and one.launches[0].grad_src == solo.launches[0].grad_src
