@@ -71,6 +71,15 @@ def hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
+    capture of this kernel (profiles/ncu_summary.json), or None if that shape was not captured."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))[kernel]["traffic_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler(threading.Thread):
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
@@ -409,6 +418,7 @@ def main():
     launches0 = K.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ps.profile = world > 1
     ev[0].record()
     for i in range(args.steps):
         if world == 1:
@@ -419,6 +429,8 @@ def main():
             ps.step()
     ev[1].record()
     sync()
+    phases = ps.phase_ms() if world > 1 else None
+    ps.profile = False
     clocks = sampler.finish()
     launches = K.launch_count() - launches0
     ms_total = reduce_max(ev[0].elapsed_time(ev[1]))
@@ -432,19 +444,31 @@ def main():
         k_ms = None
     peak, peak_src = hbm_peak()
     roofline = None
+    kname = f"dense_apply_kernel<{opt},W={W}>"
     if k_ms:
         ach = bytes_launch / k_ms / 1e6
         roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                    "traffic": None, "kernel": f"dense_apply_kernel<{opt},W={W}>", "peak_source": peak_src,
+                    "traffic": ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
                     "launches_per_step": n_kernels_step}
+    elif phases and n_kernels_step:
+        # N > 1: the apply kernels read G-1 of their G partial sums (or W - W/G gradients) over NVLink,
+        # so HBM is not their bound; the figure is reported against it for continuity only
+        k_ms = phases["apply"] / n_kernels_step
+        ach = bytes_launch / k_ms / 1e6
+        roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                    "traffic": None, "kernel": kname + " (peer loads/stores: NVLink-bound at N>1)", "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
+                    "launches_per_step": n_kernels_step, "phases_ms": {k: round(v, 4) for k, v in phases.items()}}
 
     # ---- end to end with HOST buffers ----
     e2e = None
     if not args.no_e2e:
         P = ps.plan.P
         hg = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
-        ho = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
+        # pull: one pinned host replica per GPU, shared by the workers placed on it (exactly as they
+        # share the device replica)
+        ho = {ps.plan.local_workers[0]: torch.empty(P, dtype=torch.float32).pin_memory()} if ps.plan.local_workers else {}
         for w in hg:
             hg[w].copy_(ps.grad_buffer(w))
         sync()
@@ -461,9 +485,11 @@ def main():
         e_ms = reduce_max(a.elapsed_time(b)) / n_e2e
         # whole-job bytes (every rank moves its own workers' buffers)
         e2e = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
-               "d2h_bytes_per_step": 4 * P * W, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
+               "d2h_bytes_per_step": 4 * P * world, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
                "ps_steps_per_sec": round(1e3 / e_ms, 3),
-               "api": "b200ps.ParameterServer.step_host (pinned host gradients in, pulled parameters out per worker)"}
+               "pcie_bound_ms": round(4 * P * len(ps.plan.local_workers) / 55e6, 2),
+               "api": "b200ps.ParameterServer.step_host (every worker's pinned host gradient in, pulled parameters out "
+                      "to one pinned host replica per GPU)"}
         del hg, ho
 
     # ---- CPU baseline (rank 0, N = 1 only) ----

@@ -151,6 +151,8 @@ class ParameterServer:
         self.rank, self.world, self.group, self.transport = rank, world, group, transport
         self.chunk = max(1024, chunk_elems // 1024 * 1024)
         self.t = 0
+        self.profile = False  # True: step() brackets its phases with CUDA events (see phase_ms)
+        self._events: Dict[str, List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = {"fold": [], "apply": []}
         P = self.plan.P
         self.arena = Arena(self.plan.arena_elems)
         self.replica = self.arena.tensor[:P]
@@ -267,13 +269,34 @@ class ParameterServer:
         if self.plan.two_level and self.plan.local_workers:
             # local half of the aggregation: one partial sum per GPU, before anything crosses NVLink
             bufs = _ptrs([self.grads[w].data_ptr() for w in self.plan.local_workers])
+            e0 = self._mark()
             check(lib.b200ps_dense_fold(C.c_void_p(self.partial.data_ptr()), bufs, len(self.plan.local_workers),
                                         self.plan.P, self._stream()))
+            self._mark("fold", e0)
         self._barrier()  # every worker's gradient (or every GPU's partial sum) is in place
+        e0 = self._mark()
         for L in self.plan.launches:
             if L.end > L.begin:
                 self._launch(L, L.begin, L.end, a)
+        self._mark("apply", e0)
         self._barrier()  # every replica holds every updated slice
+
+    def _mark(self, phase: Optional[str] = None, start=None):
+        if not self.profile:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        if phase is not None:
+            self._events[phase].append((start, e))
+        return e
+
+    def phase_ms(self, reset: bool = True) -> Dict[str, float]:
+        """Mean device time per step of the phases recorded while `profile` was on (synchronises)."""
+        torch.cuda.synchronize()
+        out = {k: (sum(a.elapsed_time(b) for a, b in v) / len(v) if v else 0.0) for k, v in self._events.items()}
+        if reset:
+            self._events = {k: [] for k in self._events}
+        return out
 
     def _step_nccl(self, a):
         import torch.distributed as dist
