@@ -168,8 +168,9 @@ void ps_dense_adam(float* p, float* m, float* v, const float* const* grads, int 
 
 void ps_gather(float* out, const float* table, const int64_t* ids, uint64_t n, int dim,
                int64_t row_base) {
-    uint64_t k;
-    for (k = 0; k < n; ++k)
+    int64_t k;
+#pragma omp parallel for schedule(static)
+    for (k = 0; k < (int64_t)n; ++k)
         memcpy(out + k * (uint64_t)dim, table + (uint64_t)(ids[k] - row_base) * (uint64_t)dim,
                sizeof(float) * (size_t)dim);
 }
@@ -193,11 +194,32 @@ typedef struct {
     uint32_t src;
 } keyed_t;
 
-static int keyed_cmp(const void* a, const void* b) {
-    const keyed_t *x = (const keyed_t*)a, *y = (const keyed_t*)b;
-    if (x->id != y->id) return x->id < y->id ? -1 : 1;
-    if (x->src != y->src) return x->src < y->src ? -1 : 1; /* stability: (worker, position) */
-    return 0;
+/* Stable LSD radix sort of (id, src) by id, 16 bits per pass (src ascends in the input, so a
+ * stable sort by id alone gives the (id, worker, position) order). */
+static void keyed_sort(keyed_t* a, uint64_t n) {
+    keyed_t* b = (keyed_t*)malloc(n * sizeof(keyed_t));
+    uint64_t* cnt = (uint64_t*)malloc(65537 * sizeof(uint64_t));
+    uint64_t k, maxid = 0;
+    int shift;
+    for (k = 0; k < n; ++k)
+        if ((uint64_t)a[k].id > maxid) maxid = (uint64_t)a[k].id;
+    for (shift = 0; shift < 64 && (shift == 0 || (maxid >> shift) != 0); shift += 16) {
+        keyed_t* t;
+        memset(cnt, 0, 65537 * sizeof(uint64_t));
+        for (k = 0; k < n; ++k) cnt[(((uint64_t)a[k].id >> shift) & 0xFFFF) + 1]++;
+        for (k = 0; k < 65536; ++k) cnt[k + 1] += cnt[k];
+        for (k = 0; k < n; ++k) b[cnt[((uint64_t)a[k].id >> shift) & 0xFFFF]++] = a[k];
+        t = a; a = b; b = t;
+        if (shift + 16 >= 64) { shift += 16; break; }
+    }
+    /* after an odd number of passes the result sits in the scratch buffer */
+    if (((shift / 16) & 1) != 0) {
+        memcpy(b, a, n * sizeof(keyed_t));
+        free(a);
+    } else {
+        free(b);
+    }
+    free(cnt);
 }
 
 uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, uint32_t* perm,
@@ -213,7 +235,7 @@ uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, ui
         a[k].id = ids[k];
         a[k].src = (uint32_t)k;
     }
-    qsort(a, n, sizeof(keyed_t), keyed_cmp);
+    keyed_sort(a, n);
     for (k = 0; k < n; ++k) {
         if (k == 0 || a[k].id != a[k - 1].id) {
             unique_ids[nu] = a[k].id;
@@ -250,10 +272,12 @@ static float segment_sum(const float* grad_rows, const uint32_t* perm, uint32_t 
 void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* grad_rows,
                          const uint32_t* perm, const int64_t* unique_ids,
                          const uint32_t* seg_offset, uint64_t n_unique, float inv_w, float lr) {
-    uint64_t u;
-    int d;
-    for (u = 0; u < n_unique; ++u) {
+    int64_t u;
+    /* unique ids are distinct rows, so the loop over them is parallel; the fold inside one row is not */
+#pragma omp parallel for schedule(dynamic, 64)
+    for (u = 0; u < (int64_t)n_unique; ++u) {
         float* row = table + (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+        int d;
         for (d = 0; d < dim; ++d) {
             float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w;
             row[d] = row[d] - lr * g;
@@ -265,10 +289,11 @@ void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_ba
                              const float* grad_rows, const uint32_t* perm,
                              const int64_t* unique_ids, const uint32_t* seg_offset,
                              uint64_t n_unique, float inv_w, float lr) {
-    uint64_t u;
-    int d;
-    for (u = 0; u < n_unique; ++u) {
+    int64_t u;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (u = 0; u < (int64_t)n_unique; ++u) {
         uint64_t base = (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+        int d;
         for (d = 0; d < dim; ++d) {
             float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w, an;
             an = accum[base + d] + g * g;
