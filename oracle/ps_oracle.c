@@ -253,20 +253,29 @@ uint64_t ps_sort_segment(const int64_t* ids, uint64_t n, int64_t* sorted_ids, ui
 
 /* ---------------------------------------------------------------- a12: segmented apply */
 
-/* Fixed-order segment sum of one column.  Segments of at most PS_SEG_CHUNK entries are a plain left
- * fold in sorted order; longer ones (hot ids under Zipf skew) are folded chunk by chunk -- each chunk
- * of PS_SEG_CHUNK consecutive entries left to right, then the chunk sums left to right -- so that a
- * GPU can give the chunks of one hot row to different warps and still produce these bits. */
-static float segment_sum(const float* grad_rows, const uint32_t* perm, uint32_t a, uint32_t b, int dim, int d) {
-    float total = 0.0f;
+/* Fixed-order segment sum of every column of one unique id, into total[dim].  Per column: segments
+ * of at most PS_SEG_CHUNK entries are a plain left fold in sorted order; longer ones (hot ids under
+ * Zipf skew) are folded chunk by chunk -- each chunk of PS_SEG_CHUNK consecutive entries left to
+ * right, then the chunk sums left to right -- so that a GPU can give the chunks of one hot row to
+ * different warps and still produce these bits.  (Rows are walked once, all columns together; the
+ * columns are independent, so this is the same arithmetic as folding each column on its own.) */
+static void segment_sum(float* total, float* acc, const float* grad_rows, const uint32_t* perm, uint32_t a, uint32_t b,
+                        int dim) {
     uint32_t c0, j;
+    int d;
     for (c0 = a; c0 < b; c0 += PS_SEG_CHUNK) {
         uint32_t c1 = b - c0 < PS_SEG_CHUNK ? b : c0 + PS_SEG_CHUNK;
-        float acc = grad_rows[(uint64_t)perm[c0] * (uint64_t)dim + (uint64_t)d];
-        for (j = c0 + 1; j < c1; ++j) acc = acc + grad_rows[(uint64_t)perm[j] * (uint64_t)dim + (uint64_t)d];
-        total = (c0 == a) ? acc : total + acc;
+        const float* r = grad_rows + (uint64_t)perm[c0] * (uint64_t)dim;
+        for (d = 0; d < dim; ++d) acc[d] = r[d];
+        for (j = c0 + 1; j < c1; ++j) {
+            r = grad_rows + (uint64_t)perm[j] * (uint64_t)dim;
+            for (d = 0; d < dim; ++d) acc[d] = acc[d] + r[d];
+        }
+        if (c0 == a)
+            for (d = 0; d < dim; ++d) total[d] = acc[d];
+        else
+            for (d = 0; d < dim; ++d) total[d] = total[d] + acc[d];
     }
-    return total;
 }
 
 void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* grad_rows,
@@ -274,14 +283,21 @@ void ps_sparse_apply_sgd(float* table, int dim, int64_t row_base, const float* g
                          const uint32_t* seg_offset, uint64_t n_unique, float inv_w, float lr) {
     int64_t u;
     /* unique ids are distinct rows, so the loop over them is parallel; the fold inside one row is not */
-#pragma omp parallel for schedule(dynamic, 64)
-    for (u = 0; u < (int64_t)n_unique; ++u) {
-        float* row = table + (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
-        int d;
-        for (d = 0; d < dim; ++d) {
-            float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w;
-            row[d] = row[d] - lr * g;
+#pragma omp parallel
+    {
+        float* total = (float*)malloc(2 * (size_t)dim * sizeof(float));
+        float* acc = total + dim;
+#pragma omp for schedule(dynamic, 64)
+        for (u = 0; u < (int64_t)n_unique; ++u) {
+            float* row = table + (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+            int d;
+            segment_sum(total, acc, grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim);
+            for (d = 0; d < dim; ++d) {
+                float g = total[d] * inv_w;
+                row[d] = row[d] - lr * g;
+            }
         }
+        free(total);
     }
 }
 
@@ -290,15 +306,22 @@ void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_ba
                              const int64_t* unique_ids, const uint32_t* seg_offset,
                              uint64_t n_unique, float inv_w, float lr) {
     int64_t u;
-#pragma omp parallel for schedule(dynamic, 64)
-    for (u = 0; u < (int64_t)n_unique; ++u) {
-        uint64_t base = (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
-        int d;
-        for (d = 0; d < dim; ++d) {
-            float g = segment_sum(grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim, d) * inv_w, an;
-            an = accum[base + d] + g * g;
-            accum[base + d] = an;
-            table[base + d] = table[base + d] - (lr * g) / sqrtf(an);
+#pragma omp parallel
+    {
+        float* total = (float*)malloc(2 * (size_t)dim * sizeof(float));
+        float* acc = total + dim;
+#pragma omp for schedule(dynamic, 64)
+        for (u = 0; u < (int64_t)n_unique; ++u) {
+            uint64_t base = (uint64_t)(unique_ids[u] - row_base) * (uint64_t)dim;
+            int d;
+            segment_sum(total, acc, grad_rows, perm, seg_offset[u], seg_offset[u + 1], dim);
+            for (d = 0; d < dim; ++d) {
+                float g = total[d] * inv_w, an;
+                an = accum[base + d] + g * g;
+                accum[base + d] = an;
+                table[base + d] = table[base + d] - (lr * g) / sqrtf(an);
+            }
         }
+        free(total);
     }
 }
