@@ -268,12 +268,14 @@ def sparse_arm(args):
             torch.cuda.synchronize()
 
     def step(ev=None):
+        tab._barrier()
         if ev:
             ev[0].record()
-        for w in tab.local_workers:
-            tab.pull(w, outs[w])
+        tab.serve()  # pull: every owner serves its rows to all workers, one launch per GPU
         if ev:
             ev[1].record()
+        if world > 1:
+            tab.route()  # push: rows owned elsewhere are stored into the owners' staging slots
         tab._barrier()
         tab.sort_segment()
         if ev:
@@ -308,7 +310,7 @@ def sparse_arm(args):
     s_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
     p_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
     d4 = 4 * dim
-    gather_bytes = len(tab.local_workers) * B * (8 + 2 * d4)
+    gather_bytes = W * B * 8 + (plan["n_kept"] + len(tab.local_workers) * B) * d4  # ids scanned, rows served (read) + landed (write)
     apply_bytes = plan["n_kept"] * (4 + d4) + plan["n_unique"] * (2 * d4 + 4)  # perm + rows; unique id + row R/W
     peak, peak_src = hbm_peak()
     e2e = None
@@ -324,9 +326,9 @@ def sparse_arm(args):
             for w in tab.local_workers:
                 tab.ids[w].copy_(h_ids[w], non_blocking=True)
                 tab.grad_rows[w].copy_(h_gr[w], non_blocking=True)
+            tab.pull_step()
             for w in tab.local_workers:
-                tab.pull(w, outs[w])
-                h_out[w].copy_(outs[w], non_blocking=True)
+                h_out[w].copy_(tab.pulled[w], non_blocking=True)
             tab.push_step()
 
         for _ in range(3):
@@ -359,9 +361,9 @@ def sparse_arm(args):
                        "longest_segment": int(plan["seg_offset"][1:].astype("int64").__sub__(plan["seg_offset"][:-1]).max()),
                        "l2": "table 2.56 GB and 0.54 GB of gradient rows per step exceed L2; no flush"},
             "ps_steps_per_sec": round(1e3 / ms, 3),
-            "phases_ms": {"gather_all_local_workers": round(g_ms, 4), "sort_segment": round(s_ms, 4), "apply": round(p_ms, 4)},
+            "phases_ms": {"serve_pull": round(g_ms, 4), "route+barrier+sort_segment": round(s_ms, 4), "apply": round(p_ms, 4)},
             "roofline": {"bound": "hbm", "achieved": round(gather_bytes / g_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(gather_bytes / g_ms / 1e6 / peak, 4), "traffic": None, "kernel": "sparse_gather_kernel<16>",
+                         "frac": round(gather_bytes / g_ms / 1e6 / peak, 4), "traffic": None, "kernel": "sparse_serve_kernel<16>",
                          "peak_source": peak_src, "algorithmic_bytes_per_step": gather_bytes},
             "roofline_apply": {"bound": "hbm", "achieved": round(apply_bytes / p_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
                                "frac": round(apply_bytes / p_ms / 1e6 / peak, 4), "kernel": "sparse_apply_kernel<16,sgd>",

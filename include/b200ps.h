@@ -193,6 +193,19 @@ typedef struct {
 
 int b200ps_sparse_gather(float* d_out, const float* const* d_shard_base, const b200ps_table_geom_t* geom,
                          const int64_t* d_ids, uint64_t n, void* stream);
+/* Multi-GPU routing with posted NVLink writes (rows never travel as peer reads).
+ * serve: the owner side of pull, for ALL workers at once -- this GPU walks every worker's ids,
+ *   reads the rows of its own shards from local HBM and stores them into d_out[w] (worker w's
+ *   [ids_per_worker, dim] buffer, a peer pointer when w lives elsewhere).  Every GPU of the box
+ *   runs it; together they fill every d_out[w].  On one GPU it is the batched gather.
+ * route: the worker side of push -- stores each gradient row whose id another GPU owns into
+ *   d_dst_by_gpu[owner] + k*dim (that GPU's staging slot for this worker, k = position), so the
+ *   owner's apply reads only local memory: it is given the staging slot as d_grad_rows[w] for
+ *   every worker w that lives on another GPU. */
+int b200ps_sparse_serve(float* const* d_out, const float* const* d_shard_base, const int64_t* const* d_ids,
+                        int W, uint64_t ids_per_worker, const b200ps_table_geom_t* geom, void* stream);
+int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_ids, uint64_t n,
+                        const b200ps_table_geom_t* geom, float* const* d_dst_by_gpu, void* stream);
 /* scratch for one push of n_total = W * ids_per_worker entries of a table with `dim` floats per
  * row (256-byte aligned device memory the caller owns; it holds the plan the apply call reads,
  * plus the per-chunk partial rows the apply call uses for ids with more than 256 entries) */

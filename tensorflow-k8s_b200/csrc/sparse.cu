@@ -874,3 +874,183 @@ extern "C" int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const 
         return rc;
     return b200ps_sparse_apply_sgd(d_shard_base, d_grad_rows, W, ids_per_worker, geom, lr, scratch, stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU routing with posted NVLink writes.
+//
+// A random 256-byte read from peer memory exposes the full NVLink round trip (~3 us) per row and
+// ran at ~90 GB/s; a write is posted and streams.  So rows never travel as peer reads:
+//   pull  `serve`: the OWNER of a shard walks every worker's ids (streamed, local or peer), reads
+//         the rows it owns from its local HBM and writes them into the requesting worker's output
+//         buffer (a peer store when that worker lives on another GPU).  One launch serves all
+//         workers; on one GPU it is simply the batched gather.
+//   push  `route`: the WORKER's GPU walks its own ids and gradient rows and stores every row owned
+//         by another GPU into that GPU's staging slot for this worker; the owner's apply then
+//         reads local memory only.
+// ------------------------------------------------------------------------------------------------
+namespace b200ps {
+namespace {
+
+struct ServeArgs {
+    float* out[B200PS_MAX_WORKERS];  // worker w's pulled rows [B, dim]
+};
+
+template <int LG>
+__global__ void __launch_bounds__(256) sparse_serve_kernel(const __grid_constant__ ServeArgs sa,
+                                                           const __grid_constant__ ShardBases tb,
+                                                           const __grid_constant__ IdSources src,
+                                                           const __grid_constant__ Geom g) {
+    constexpr int R = 4;
+    const int lane = threadIdx.x % LG;
+    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint32_t e0 = group; e0 < src.n_total; e0 += R * ngroups) {
+        const float4* rd[R];
+        float4* wr[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t e = e0 + r * ngroups;
+            rd[r] = nullptr;
+            wr[r] = nullptr;
+            if (e < src.n_total) {
+                const uint32_t w = e / src.per_worker, pos = e - w * src.per_worker;
+                const int64_t id = src.ids[w][pos];
+                const bool in_range = id >= 0 && (uint64_t)id < g.rows;
+                uint64_t lrow = 0;
+                const int s = in_range ? owner_of(g, (uint64_t)id, &lrow) : 0;
+                // an out-of-range id belongs to nobody: the GPU of shard 0 answers it with zeros
+                if (s % g.world == g.rank) {
+                    wr[r] = reinterpret_cast<float4*>(sa.out[w] + (uint64_t)pos * (uint64_t)g.dim);
+                    if (in_range) rd[r] = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
+                }
+            }
+        }
+        for (int c = lane; c < dim4; c += LG) {
+            float4 v[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) v[r] = rd[r] ? rd[r][c] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (wr[r]) wr[r][c] = v[r];
+        }
+    }
+}
+
+struct RouteArgs {
+    float* dst[B200PS_MAX_MIRRORS + 1];  // per GPU: its staging slot for this worker (null for this GPU)
+};
+
+template <int LG>
+__global__ void __launch_bounds__(256) sparse_route_kernel(const __grid_constant__ RouteArgs ra,
+                                                           const float* __restrict__ grad_rows,
+                                                           const int64_t* __restrict__ ids, uint32_t n,
+                                                           const __grid_constant__ Geom g) {
+    constexpr int R = 4;
+    const int lane = threadIdx.x % LG;
+    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int dim4 = g.dim / 4;
+    for (uint32_t k0 = group; k0 < n; k0 += R * ngroups) {
+        float4* wr[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t k = k0 + r * ngroups;
+            wr[r] = nullptr;
+            if (k < n) {
+                const int64_t id = ids[k];
+                if (id >= 0 && (uint64_t)id < g.rows) {
+                    uint64_t lrow;
+                    const int o = owner_of(g, (uint64_t)id, &lrow) % g.world;
+                    if (o != g.rank) wr[r] = reinterpret_cast<float4*>(ra.dst[o] + (uint64_t)k * (uint64_t)g.dim);
+                }
+            }
+        }
+        for (int c = lane; c < dim4; c += LG) {
+            float4 v[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (wr[r]) v[r] = ldg_row4(grad_rows + (uint64_t)(k0 + r * ngroups) * (uint64_t)g.dim, c);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (wr[r]) wr[r][c] = v[r];
+        }
+    }
+}
+
+}  // namespace
+}  // namespace b200ps
+
+extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_shard_base, const int64_t* const* d_ids,
+                                   int W, uint64_t ids_per_worker, const b200ps_table_geom_t* geom, void* stream) {
+    Geom g;
+    if (int rc = make_geom(geom, &g)) return rc;
+    B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS && d_out && d_ids && d_shard_base, B200PS_ERR_INVALID,
+                   "bad worker count or null argument");
+    const uint64_t n = (uint64_t)W * ids_per_worker;
+    B200PS_REQUIRE(n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be below 2^32");
+    if (n == 0) return B200PS_OK;
+    ServeArgs sa{};
+    IdSources src{};
+    src.per_worker = (uint32_t)ids_per_worker;
+    src.n_total = (uint32_t)n;
+    for (int w = 0; w < W; ++w) {
+        B200PS_REQUIRE(d_out[w] && ((uintptr_t)d_out[w] & 15) == 0 && d_ids[w], B200PS_ERR_INVALID,
+                       "output / ids of worker %d: null or not 16-byte aligned", w);
+        sa.out[w] = d_out[w];
+        src.ids[w] = d_ids[w];
+    }
+    ShardBases tb{};
+    for (int s = 0; s < g.nshards; ++s) {
+        tb.base[s] = const_cast<float*>(d_shard_base[s]);
+        if (s % g.world == g.rank)
+            B200PS_REQUIRE(d_shard_base[s] && ((uintptr_t)d_shard_base[s] & 15) == 0, B200PS_ERR_INVALID,
+                           "table shard %d must be a 16-byte aligned device pointer", s);
+    }
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const int lg = lane_group(g.dim);
+    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
+    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (lg) {
+        case 4: sparse_serve_kernel<4><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
+        case 8: sparse_serve_kernel<8><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
+        case 16: sparse_serve_kernel<16><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
+        default: sparse_serve_kernel<32><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
+    }
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_ids, uint64_t n,
+                                   const b200ps_table_geom_t* geom, float* const* d_dst_by_gpu, void* stream) {
+    Geom g;
+    if (int rc = make_geom(geom, &g)) return rc;
+    B200PS_REQUIRE(g.world <= B200PS_MAX_MIRRORS + 1, B200PS_ERR_RANGE, "at most %d GPUs", B200PS_MAX_MIRRORS + 1);
+    B200PS_REQUIRE(n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "n must be below 2^32");
+    if (n == 0 || g.world == 1) return B200PS_OK;  // nothing lives elsewhere
+    B200PS_REQUIRE(d_grad_rows && d_ids && d_dst_by_gpu && ((uintptr_t)d_grad_rows & 15) == 0, B200PS_ERR_INVALID,
+                   "null or misaligned argument");
+    RouteArgs ra{};
+    for (int o = 0; o < g.world; ++o) {
+        if (o == g.rank) continue;
+        B200PS_REQUIRE(d_dst_by_gpu[o] && ((uintptr_t)d_dst_by_gpu[o] & 15) == 0, B200PS_ERR_INVALID,
+                       "staging slot on GPU %d: null or not 16-byte aligned", o);
+        ra.dst[o] = d_dst_by_gpu[o];
+    }
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const int lg = lane_group(g.dim);
+    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
+    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (lg) {
+        case 4: sparse_route_kernel<4><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
+        case 8: sparse_route_kernel<8><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
+        case 16: sparse_route_kernel<16><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
+        default: sparse_route_kernel<32><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
+    }
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}

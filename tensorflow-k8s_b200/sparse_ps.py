@@ -4,13 +4,15 @@ An embedding table of `rows` x `dim` fp32 is partitioned by TF "div" over S PS s
 lives on GPU s mod G, compute task w on GPU w mod G.  Each rank keeps one exported arena:
 
     [ rows of local shard 0 | local shard 1 | ... | (Adagrad accumulators, same order) |
-      per local worker: ids int64[B] | gradient rows fp32[B, dim] ]
+      per local worker: ids int64[B] | gradient rows fp32[B, dim] | pulled rows fp32[B, dim] |
+      per REMOTE worker: staging fp32[B, dim] for the gradient rows it routes here ]
 
 Every rank can compute every other rank's layout, so after the one-time handle exchange a kernel
-is given plain base pointers: `pull` gathers rows straight out of the owning GPUs' shards, and
-`push_step` lets each GPU sort the ids of ITS shards out of all workers' id buffers and fold the
-matching gradient rows from wherever the workers left them -- the routing all-to-alls of a
-classic PS are NVLink loads inside the kernels.
+is given plain base pointers, and the routing all-to-alls of a classic PS are fused into kernels:
+ids are streamed from wherever the workers wrote them, and rows cross NVLink only as posted
+stores -- `pull_step`: each owner serves the rows of its shards into the requesting workers'
+buffers; `push_step`: each worker's GPU routes the rows other GPUs own into their staging slots,
+then every GPU sorts the ids of ITS shards and folds rows out of local memory only.
 
 Reference: none (TensorFlow's embedding_lookup / sparse apply ops inside the containers a TFJob
 launches); roles per k8s-operator.md:6.  torch is plumbing (streams, distributed rendezvous).
@@ -49,6 +51,8 @@ class TableLayout:
         self.accum_off: Dict[int, int] = {}
         self.ids_off: Dict[int, int] = {}
         self.grad_off: Dict[int, int] = {}
+        self.out_off: Dict[int, int] = {}
+        self.stage_off: Dict[Tuple[int, int], int] = {}
         self.arena_bytes: List[int] = []
         for r in range(world):
             off = 0
@@ -64,6 +68,11 @@ class TableLayout:
                 self.ids_off[w] = off
                 off += _up(B * 8)
                 self.grad_off[w] = off
+                off += _up(B * dim * 4)
+                self.out_off[w] = off
+                off += _up(B * dim * 4)
+            for w in (w for w in range(W) if placement_gpu(w, world) != r):
+                self.stage_off[(r, w)] = off  # rows worker w routes to GPU r
                 off += _up(B * dim * 4)
             self.arena_bytes.append(max(off, 256))
 
@@ -104,9 +113,11 @@ class EmbeddingTable:
                 self.accums[s].fill_(accum_init)
         self.ids: Dict[int, torch.Tensor] = {}
         self.grad_rows: Dict[int, torch.Tensor] = {}
+        self.pulled: Dict[int, torch.Tensor] = {}
         for w in self.local_workers:
             self.ids[w] = torch.as_tensor(_ByteArray(p.value + self.lay.ids_off[w], B * 8, "<i8", (B,)), device=dev)
             self.grad_rows[w] = torch.as_tensor(_ByteArray(p.value + self.lay.grad_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
+            self.pulled[w] = torch.as_tensor(_ByteArray(p.value + self.lay.out_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
         self.workspace = torch.empty(int(lib.b200ps_sparse_workspace_bytes(num_workers * B, dim)), dtype=torch.uint8, device=dev)
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
         if world > 1:
@@ -116,7 +127,12 @@ class EmbeddingTable:
         self._accum_ptrs = (C.c_void_p * num_shards)(*[(self.base[L.shard_rank(s)] + L.accum_off[s]) if L.adagrad else 0
                                                        for s in range(num_shards)])
         self._ids_ptrs = (C.c_void_p * num_workers)(*[self.base[L.worker_rank(w)] + L.ids_off[w] for w in range(num_workers)])
-        self._grad_ptrs = (C.c_void_p * num_workers)(*[self.base[L.worker_rank(w)] + L.grad_off[w] for w in range(num_workers)])
+        # apply reads local memory only: a local worker's own buffer, or this GPU's staging slot for a remote one
+        self._grad_ptrs = (C.c_void_p * num_workers)(*[
+            self.base[rank] + (L.grad_off[w] if L.worker_rank(w) == rank else L.stage_off[(rank, w)]) for w in range(num_workers)])
+        self._out_ptrs = (C.c_void_p * num_workers)(*[self.base[L.worker_rank(w)] + L.out_off[w] for w in range(num_workers)])
+        self._route_dst = {w: (C.c_void_p * world)(*[0 if o == rank else self.base[o] + L.stage_off[(o, w)] for o in range(world)])
+                           for w in self.local_workers}
 
     def _exchange_handles(self):
         import torch.distributed as dist
@@ -136,7 +152,7 @@ class EmbeddingTable:
         for r, b in list(self.base.items()):
             if r != self.rank:
                 lib.b200ps_ipc_close(C.c_void_p(b))
-        self.shards, self.accums, self.ids, self.grad_rows = {}, {}, {}, {}
+        self.shards, self.accums, self.ids, self.grad_rows, self.pulled = {}, {}, {}, {}, {}
         if self._own:
             check(lib.b200ps_dev_free(C.c_void_p(self._own)))
             self._own = 0
@@ -166,6 +182,24 @@ class EmbeddingTable:
                                        C.c_void_p(self.ids[worker].data_ptr()), self.lay.B, self._stream()))
         return out
 
+    def serve(self):
+        """Owner side of pull for every worker: rows of this GPU's shards -> the workers' `pulled` buffers."""
+        check(lib.b200ps_sparse_serve(self._out_ptrs, self._shard_ptrs, self._ids_ptrs, self.lay.W, self.lay.B,
+                                      C.byref(self.geom), self._stream()))
+
+    def pull_step(self):
+        """a10 for all workers of the job at once (collective): afterwards `pulled[w]` holds
+        table[ids_w] for every local worker w."""
+        self._barrier()  # every worker's ids are written
+        self.serve()
+        self._barrier()  # every owner has delivered its rows
+
+    def route(self):
+        """Worker side of push: gradient rows owned by other GPUs go to their staging slots."""
+        for w in self.local_workers:
+            check(lib.b200ps_sparse_route(C.c_void_p(self.grad_rows[w].data_ptr()), C.c_void_p(self.ids[w].data_ptr()),
+                                          self.lay.B, C.byref(self.geom), self._route_dst[w], self._stream()))
+
     def sort_segment(self):
         """a11: the plan (sorted ids, permutation, segments) of this GPU's shards, into the workspace."""
         check(lib.b200ps_sparse_sort_segment(self._ids_ptrs, self.lay.W, self.lay.B, C.byref(self.geom),
@@ -183,7 +217,9 @@ class EmbeddingTable:
 
     def push_step(self):
         """a11 + a12 for the shards of this GPU over every worker's (ids, gradient rows)."""
-        self._barrier()  # all workers' ids and gradient rows are written
+        if self.world > 1:
+            self.route()
+        self._barrier()  # all workers' ids are written and every routed row has landed
         self.sort_segment()
         self.apply()
         self._barrier()  # every shard is updated before anyone pulls again

@@ -31,9 +31,10 @@ def main():
         for w in tab.local_workers:
             tab.ids[w].copy_(torch.from_numpy(ids[w]))
             tab.grad_rows[w].copy_(torch.from_numpy(grad[w]))
-        tab._barrier()
-        for w in tab.local_workers:  # rows come from the owning GPUs' shards
-            tab.pull(w, out)
+        tab.pull_step()  # owners serve rows into the workers' buffers (posted NVLink stores)
+        for w in tab.local_workers:
+            ok = ok and np.array_equal(tab.pulled[w].cpu().numpy().view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
+            tab.pull(w, out)  # the single-worker form reads peer shards directly
             ok = ok and np.array_equal(out.cpu().numpy().view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
         tab.push_step()
         inv_w = np.float32(1.0) / np.float32(W)

@@ -206,6 +206,9 @@ def test_embedding_table_host_api(oracle, opt, kind):
         for w in (0, W - 1):
             tab.pull(w, out)
             assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.gather(table, ids[w]).view(np.uint32))
+        tab.pull_step()  # all workers in one launch
+        for w in range(W):
+            assert np.array_equal(tab.pulled[w].cpu().numpy().view(np.uint32), oracle.gather(table, ids[w]).view(np.uint32))
         tab.push_step()
         if opt == "sgd":
             oracle.sparse_apply_sgd(table, 0, grad.reshape(-1, dim), ids.reshape(-1), np.float32(1.0) / np.float32(W), np.float32(0.05))

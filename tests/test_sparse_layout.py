@@ -11,9 +11,12 @@ def test_layout_c2_two_gpus():
     assert L.shard_off[0] == 0 and L.shard_off[2] == shard_bytes and L.shard_off[1] == 0
     assert L.accum_off[0] == 4 * shard_bytes and L.ids_off[0] == 8 * shard_bytes
     assert L.grad_off[0] == L.ids_off[0] + 262_144 * 8
-    assert L.ids_off[2] == L.grad_off[0] + 262_144 * 64 * 4
-    assert L.arena_bytes[0] == L.arena_bytes[1] == L.grad_off[6] + 262_144 * 64 * 4
-    assert all(v % 256 == 0 for d in (L.shard_off, L.accum_off, L.ids_off, L.grad_off) for v in d.values())
+    rows_bytes = 262_144 * 64 * 4
+    assert L.out_off[0] == L.grad_off[0] + rows_bytes and L.ids_off[2] == L.out_off[0] + rows_bytes
+    # after the 4 local workers: one staging slot per remote worker (1, 3, 5, 7 on rank 0)
+    assert L.stage_off[(0, 1)] == L.out_off[6] + rows_bytes and sorted(w for r, w in L.stage_off if r == 0) == [1, 3, 5, 7]
+    assert L.arena_bytes[0] == L.arena_bytes[1] == L.stage_off[(0, 7)] + rows_bytes
+    assert all(v % 256 == 0 for d in (L.shard_off, L.accum_off, L.ids_off, L.grad_off, L.out_off, L.stage_off) for v in d.values())
 
 
 def test_layout_uneven():
