@@ -562,6 +562,17 @@ __global__ void __launch_bounds__(256) sparse_gather_kernel(float* __restrict__ 
     }
 }
 
+// grid for a grid-stride kernel: exactly the CTAs that are resident at once (SMs x occupancy), so
+// there is no partial last wave; capped by the work available
+template <typename Kern>
+int resident_grid(Kern kern, int threads, uint64_t want_blocks) {
+    int sms = 0, per_sm = 0;
+    if (sm_count(&sms) != cudaSuccess) sms = 148;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+    const uint64_t cap = (uint64_t)sms * (uint64_t)per_sm;
+    return (int)(want_blocks < cap ? (want_blocks ? want_blocks : 1) : cap);
+}
+
 int lane_group(int dim) {
     const int d4 = dim / 4;
     int lg = 4;
@@ -648,13 +659,12 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     B200PS_CUDA(sm_count(&sms));
     const int lg = lane_group(g.dim);
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
-    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
     // the long-segment counters belong to this apply (a plan may be applied more than once)
     B200PS_CUDA(cudaMemsetAsync(ws.hdr + HDR_NLONG, 0, 2 * sizeof(uint32_t), st));
 #define LAUNCH_APPLY(LG)                                                      \
-    sparse_apply_kernel<LG, ADAGRAD><<<grid, 256, 0, st>>>(tb, gs, g, a);     \
-    long_partials_kernel<LG><<<sms * 8, 256, 0, st>>>(gs, g, a);              \
+    sparse_apply_kernel<LG, ADAGRAD><<<resident_grid(sparse_apply_kernel<LG, ADAGRAD>, 256, want), 256, 0, st>>>(tb, gs, g, a); \
+    long_partials_kernel<LG><<<resident_grid(long_partials_kernel<LG>, 256, want), 256, 0, st>>>(gs, g, a);              \
     long_final_kernel<LG, ADAGRAD><<<sms, 256, 0, st>>>(tb, g, a)
     switch (lg) {
         case 4: LAUNCH_APPLY(4); break;
@@ -697,12 +707,16 @@ extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_ba
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_GATHER(LG) \
+    sparse_gather_kernel<LG><<<resident_grid(sparse_gather_kernel<LG>, 256, want), 256, 0, st>>>(d_out, tb, g, d_ids, n)
     switch (lg) {
-        case 4: sparse_gather_kernel<4><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
-        case 8: sparse_gather_kernel<8><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
-        case 16: sparse_gather_kernel<16><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
-        default: sparse_gather_kernel<32><<<grid, 256, 0, st>>>(d_out, tb, g, d_ids, n); break;
+        case 4: LAUNCH_GATHER(4); break;
+        case 8: LAUNCH_GATHER(8); break;
+        case 16: LAUNCH_GATHER(16); break;
+        default: LAUNCH_GATHER(32); break;
     }
+#undef LAUNCH_GATHER
+    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -896,7 +910,7 @@ struct ServeArgs {
 };
 
 template <int LG>
-__global__ void __launch_bounds__(256) sparse_serve_kernel(const __grid_constant__ ServeArgs sa,
+__global__ void __launch_bounds__(256, 4) sparse_serve_kernel(const __grid_constant__ ServeArgs sa,
                                                            const __grid_constant__ ShardBases tb,
                                                            const __grid_constant__ IdSources src,
                                                            const __grid_constant__ Geom g) {
@@ -941,7 +955,7 @@ struct RouteArgs {
 };
 
 template <int LG>
-__global__ void __launch_bounds__(256) sparse_route_kernel(const __grid_constant__ RouteArgs ra,
+__global__ void __launch_bounds__(256, 4) sparse_route_kernel(const __grid_constant__ RouteArgs ra,
                                                            const float* __restrict__ grad_rows,
                                                            const int64_t* __restrict__ ids, uint32_t n,
                                                            const __grid_constant__ Geom g) {
@@ -1011,12 +1025,16 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_SERVE(LG) \
+    sparse_serve_kernel<LG><<<resident_grid(sparse_serve_kernel<LG>, 256, want), 256, 0, st>>>(sa, tb, src, g)
     switch (lg) {
-        case 4: sparse_serve_kernel<4><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
-        case 8: sparse_serve_kernel<8><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
-        case 16: sparse_serve_kernel<16><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
-        default: sparse_serve_kernel<32><<<grid, 256, 0, st>>>(sa, tb, src, g); break;
+        case 4: LAUNCH_SERVE(4); break;
+        case 8: LAUNCH_SERVE(8); break;
+        case 16: LAUNCH_SERVE(16); break;
+        default: LAUNCH_SERVE(32); break;
     }
+#undef LAUNCH_SERVE
+    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -1044,12 +1062,16 @@ extern "C" int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_id
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_ROUTE(LG) \
+    sparse_route_kernel<LG><<<resident_grid(sparse_route_kernel<LG>, 256, want), 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g)
     switch (lg) {
-        case 4: sparse_route_kernel<4><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
-        case 8: sparse_route_kernel<8><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
-        case 16: sparse_route_kernel<16><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
-        default: sparse_route_kernel<32><<<grid, 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g); break;
+        case 4: LAUNCH_ROUTE(4); break;
+        case 8: LAUNCH_ROUTE(8); break;
+        case 16: LAUNCH_ROUTE(16); break;
+        default: LAUNCH_ROUTE(32); break;
     }
+#undef LAUNCH_ROUTE
+    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
