@@ -22,6 +22,7 @@
 
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.h"
 #include "cuda_util.h"
@@ -47,6 +48,7 @@ struct DenseParams {
     float inv_w;
     float lr;  // SGD: lr.  Adam: lr_t.
     float beta1, beta2, omb1, omb2, eps;
+    int load_kind;  // gradient loads: 0 = nc + L1 no-allocate + L2 evict-first, 1 = plain coherent ld.global
 };
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -56,8 +58,12 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
 }
 
 // read-once stream (gradients): non-coherent path, no L1 allocation, first to leave L2
-__device__ __forceinline__ float4 ld_once(const float4* ptr, uint64_t pol) {
+__device__ __forceinline__ float4 ld_once(const float4* ptr, uint64_t pol, int kind = 0) {
     float4 r;
+    if (kind == 1) {
+        asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(ptr));
+        return r;
+    }
     asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
                  : "l"(ptr), "l"(pol));
@@ -118,7 +124,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
 #pragma unroll
         for (int w = 0; w < WT; ++w)
 #pragma unroll
-            for (int u = 0; u < U; ++u) G[w][u] = ld_once(reinterpret_cast<const float4*>(a.g[w]) + i + u * stride, pol);
+            for (int u = 0; u < U; ++u) G[w][u] = ld_once(reinterpret_cast<const float4*>(a.g[w]) + i + u * stride, pol, a.load_kind);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (OPT != OPT_FOLD) P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
@@ -141,7 +147,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
                 M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
                 V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
             }
-            acc[u] = ld_once(reinterpret_cast<const float4*>(a.g[0]) + i + u * stride, pol);
+            acc[u] = ld_once(reinterpret_cast<const float4*>(a.g[0]) + i + u * stride, pol, a.load_kind);
         }
         for (int w0 = 1; w0 < a.W; w0 += 4) {
             float4 G[4][U];
@@ -150,7 +156,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
                 if (w0 + c < a.W) {
 #pragma unroll
                     for (int u = 0; u < U; ++u)
-                        G[c][u] = ld_once(reinterpret_cast<const float4*>(a.g[w0 + c]) + i + u * stride, pol);
+                        G[c][u] = ld_once(reinterpret_cast<const float4*>(a.g[w0 + c]) + i + u * stride, pol, a.load_kind);
                 }
 #pragma unroll
             for (int c = 0; c < 4; ++c)
@@ -290,6 +296,8 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     const Tuning t = g_tuning;
+    static const int env_load_kind = getenv("B200PS_DENSE_LOAD") ? atoi(getenv("B200PS_DENSE_LOAD")) : 0;  // experiments
+    a.load_kind = env_load_kind;
     const uint64_t work = a.n4 ? a.n4 : a.n;
     uint64_t want = (work + (uint64_t)t.threads * (uint64_t)t.unroll - 1) / ((uint64_t)t.threads * (uint64_t)t.unroll);
     const uint64_t cap = (uint64_t)sms * (uint64_t)t.ctas_per_sm;
