@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--ids", default="zipf", choices=["zipf", "uniform"], help="id distribution of --workload c2")
     ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--barrier", default="peer", choices=["peer", "nccl"], help="cross-rank barrier of a step when N > 1")
     ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
@@ -252,7 +253,7 @@ def sparse_arm(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd", lr=C2["lr"], rank=rank, world=world)
+    tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd", lr=C2["lr"], rank=rank, world=world, barrier=args.barrier)
     tab.init_uniform(1)
     ids = synth.make_ids(args.ids, rows, W, B, 1)
     outs = {}
@@ -401,7 +402,7 @@ def main():
         K.set_dense_tuning(*[int(x) for x in os.environ["B200PS_DENSE_TUNING"].split(",")])
     label, sizes, S, W, opt = workload(args.workload, world)
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
-                                aggregate=args.aggregate)
+                                aggregate=args.aggregate, barrier=args.barrier)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)

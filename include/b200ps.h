@@ -162,6 +162,16 @@ int b200ps_dev_free(void* d_ptr);
 int b200ps_ipc_export(const void* d_ptr, void* handle_out /* B200PS_IPC_HANDLE_BYTES */);
 int b200ps_ipc_open(const void* handle, void** d_ptr); /* maps a peer's allocation */
 int b200ps_ipc_close(void* d_ptr);
+/* Stream-ordered barrier across the ranks through peer memory (a few microseconds; the library
+ * all-reduce it replaces costs tens).  Every rank owns B200PS_BARRIER_WORDS zero-initialised
+ * 32-bit words inside its exported arena; d_flags_by_rank[r] points at rank r's words.  All ranks
+ * call it with the same, strictly increasing `epoch` (1, 2, 3, ...).  Work queued on `stream`
+ * before the call on every rank is complete -- peer stores included -- before work queued after
+ * it on any rank starts.  The wait is bounded (~4 s); a timeout is reported by
+ * b200ps_peer_barrier_error (which synchronises the stream). */
+#define B200PS_BARRIER_WORDS 16
+int b200ps_peer_barrier(uint32_t* const* d_flags_by_rank, int rank, int world, uint32_t epoch, void* stream);
+int b200ps_peer_barrier_error(const uint32_t* d_my_flags, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Sparse group: embedding tables sharded by rows (TF "div" partitioning), SURVEY.md 8(a) rows

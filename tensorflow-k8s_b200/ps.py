@@ -31,6 +31,7 @@ from .contract import placement_gpu
 from .layout import ShardMap
 
 IPC_BYTES = 64
+BARRIER_WORDS = 16  # B200PS_BARRIER_WORDS
 
 
 # --------------------------------------------------------------------------------------------------
@@ -138,7 +139,9 @@ class ParameterServer:
     def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
                  lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
                  world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20,
-                 aggregate: str = "flat"):
+                 aggregate: str = "flat", barrier: str = "peer"):
+        if barrier not in ("peer", "nccl"):
+            raise ValueError("barrier must be 'peer' (flags in peer memory) or 'nccl' (a 4-byte all-reduce)")
         if optimizer not in ("sgd", "adam"):
             raise ValueError("optimizer must be 'sgd' or 'adam'")
         if transport not in ("peer", "nccl"):
@@ -154,7 +157,9 @@ class ParameterServer:
         self.profile = False  # True: step() brackets its phases with CUDA events (see phase_ms)
         self._events: Dict[str, List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = {"fold": [], "apply": []}
         P = self.plan.P
-        self.arena = Arena(self.plan.arena_elems)
+        self.arena = Arena(self.plan.arena_elems + BARRIER_WORDS)  # barrier flags live behind the buffers
+        self.barrier_kind, self._epoch = barrier, 0
+        self.arena.tensor[self.plan.arena_elems:].zero_()
         self.replica = self.arena.tensor[:P]
         g0 = self.plan.first_grad_slot
         self.partial = self.arena.tensor[P: 2 * P] if self.plan.two_level else None
@@ -172,8 +177,13 @@ class ParameterServer:
         self._s_in, self._s_out = torch.cuda.Stream(), torch.cuda.Stream()
         if world > 1:
             self._exchange_handles()
+            self._flag_ptrs = _ptrs([self.peer_base[r] + 4 * self.plan.arena_elems for r in range(world)])
             if transport == "nccl":
                 self._init_nccl()
+            import torch.distributed as dist
+
+            torch.cuda.synchronize()
+            dist.barrier(group=group)  # every rank has zeroed its flags and mapped every arena
 
     # ---- set-up -------------------------------------------------------------------------------
     def _exchange_handles(self):
@@ -198,6 +208,10 @@ class ParameterServer:
 
     def close(self):
         torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.barrier(group=self.group)  # nobody unmaps while a peer may still touch the arena
         for r, base in list(self.peer_base.items()):
             if r != self.rank:
                 lib.b200ps_ipc_close(C.c_void_p(base))
@@ -233,9 +247,18 @@ class ParameterServer:
         """Stream-ordered cross-rank barrier: work queued before it on every rank completes before
         work queued after it on any rank starts."""
         if self.world > 1:
-            import torch.distributed as dist
+            if self.barrier_kind == "peer":
+                self._epoch += 1
+                check(lib.b200ps_peer_barrier(self._flag_ptrs, self.rank, self.world, self._epoch, self._stream()))
+            else:
+                import torch.distributed as dist
 
-            dist.all_reduce(self._flag, group=self.group)
+                dist.all_reduce(self._flag, group=self.group)
+
+    def check_barriers(self):
+        """Raises if a peer barrier timed out (some rank never arrived).  Synchronises."""
+        if self.world > 1 and self.barrier_kind == "peer":
+            check(lib.b200ps_peer_barrier_error(C.c_void_p(self.arena.ptr + 4 * self.plan.arena_elems), self._stream()))
 
     def _opt_scalars(self) -> Optional[AdamScalars]:
         if self.optimizer != "adam":
@@ -366,6 +389,7 @@ class ParameterServer:
     # ---- inspection ---------------------------------------------------------------------------
     def dump(self) -> Dict[int, Dict[str, np.ndarray]]:
         """Local slices: {shard: {"range": (b, e), "p": ..., "m": ..., "v": ...}} as NumPy arrays."""
+        self.check_barriers()
         torch.cuda.synchronize()
         out = {}
         for L in self.plan.launches:

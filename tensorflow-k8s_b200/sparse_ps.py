@@ -30,6 +30,7 @@ from .contract import placement_gpu
 from .layout import row_range
 
 IPC_BYTES = 64
+BARRIER_WORDS = 16  # B200PS_BARRIER_WORDS
 
 
 def _up(x: int, a: int = 256) -> int:
@@ -53,6 +54,7 @@ class TableLayout:
         self.grad_off: Dict[int, int] = {}
         self.out_off: Dict[int, int] = {}
         self.stage_off: Dict[Tuple[int, int], int] = {}
+        self.flag_off: Dict[int, int] = {}
         self.arena_bytes: List[int] = []
         for r in range(world):
             off = 0
@@ -74,7 +76,9 @@ class TableLayout:
             for w in (w for w in range(W) if placement_gpu(w, world) != r):
                 self.stage_off[(r, w)] = off  # rows worker w routes to GPU r
                 off += _up(B * dim * 4)
-            self.arena_bytes.append(max(off, 256))
+            self.flag_off[r] = off  # barrier flags behind everything else
+            off += _up(BARRIER_WORDS * 4)
+            self.arena_bytes.append(off)
 
     def shard_rank(self, s: int) -> int:
         return placement_gpu(s, self.world)
@@ -86,7 +90,9 @@ class TableLayout:
 class EmbeddingTable:
     def __init__(self, rows: int, dim: int, num_shards: int, num_workers: int, ids_per_worker: int,
                  optimizer: str = "sgd", lr: float = 0.05, rank: int = 0, world: int = 1, group=None,
-                 accum_init: float = 0.1):
+                 accum_init: float = 0.1, barrier: str = "peer"):
+        if barrier not in ("peer", "nccl"):
+            raise ValueError("barrier must be 'peer' or 'nccl'")
         if optimizer not in ("sgd", "adagrad"):
             raise ValueError("optimizer must be 'sgd' or 'adagrad'")
         if not torch.cuda.is_available():
@@ -120,8 +126,15 @@ class EmbeddingTable:
             self.pulled[w] = torch.as_tensor(_ByteArray(p.value + self.lay.out_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
         self.workspace = torch.empty(int(lib.b200ps_sparse_workspace_bytes(num_workers * B, dim)), dtype=torch.uint8, device=dev)
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.barrier_kind, self._epoch = barrier, 0
+        torch.as_tensor(_ByteArray(p.value + self.lay.flag_off[rank], BARRIER_WORDS * 4, "<i4", (BARRIER_WORDS,)), device=dev).zero_()
         if world > 1:
             self._exchange_handles()
+            self._flag_ptrs = (C.c_void_p * world)(*[self.base[r] + self.lay.flag_off[r] for r in range(world)])
+            import torch.distributed as dist
+
+            torch.cuda.synchronize()
+            dist.barrier(group=group)  # flags zeroed and arenas mapped everywhere
         L = self.lay
         self._shard_ptrs = (C.c_void_p * num_shards)(*[self.base[L.shard_rank(s)] + L.shard_off[s] for s in range(num_shards)])
         self._accum_ptrs = (C.c_void_p * num_shards)(*[(self.base[L.shard_rank(s)] + L.accum_off[s]) if L.adagrad else 0
@@ -149,6 +162,10 @@ class EmbeddingTable:
 
     def close(self):
         torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.barrier(group=self.group)
         for r, b in list(self.base.items()):
             if r != self.rank:
                 lib.b200ps_ipc_close(C.c_void_p(b))
@@ -163,9 +180,17 @@ class EmbeddingTable:
 
     def _barrier(self):
         if self.world > 1:
-            import torch.distributed as dist
+            if self.barrier_kind == "peer":
+                self._epoch += 1
+                check(lib.b200ps_peer_barrier(self._flag_ptrs, self.rank, self.world, self._epoch, self._stream()))
+            else:
+                import torch.distributed as dist
 
-            dist.all_reduce(self._flag, group=self.group)
+                dist.all_reduce(self._flag, group=self.group)
+
+    def check_barriers(self):
+        if self.world > 1 and self.barrier_kind == "peer":
+            check(lib.b200ps_peer_barrier_error(C.c_void_p(self._own + self.lay.flag_off[self.rank]), self._stream()))
 
     # ---- table -------------------------------------------------------------------------------
     def init_uniform(self, seed: int = 1):
@@ -231,6 +256,7 @@ class EmbeddingTable:
         return sparse_plan_read(self.workspace, self.lay.W * self.lay.B, self.lay.rows)
 
     def dump(self) -> Dict[int, Tuple[Tuple[int, int], np.ndarray]]:
+        self.check_barriers()
         torch.cuda.synchronize()
         return {s: (self.lay.shard_range[s], self.shards[s].cpu().numpy()) for s in self.local_shards}
 

@@ -15,7 +15,7 @@ def test_layout_c2_two_gpus():
     assert L.out_off[0] == L.grad_off[0] + rows_bytes and L.ids_off[2] == L.out_off[0] + rows_bytes
     # after the 4 local workers: one staging slot per remote worker (1, 3, 5, 7 on rank 0)
     assert L.stage_off[(0, 1)] == L.out_off[6] + rows_bytes and sorted(w for r, w in L.stage_off if r == 0) == [1, 3, 5, 7]
-    assert L.arena_bytes[0] == L.arena_bytes[1] == L.stage_off[(0, 7)] + rows_bytes
+    assert L.flag_off[0] == L.stage_off[(0, 7)] + rows_bytes and L.arena_bytes[0] == L.arena_bytes[1] == L.flag_off[0] + 256
     assert all(v % 256 == 0 for d in (L.shard_off, L.accum_off, L.ids_off, L.grad_off, L.out_off, L.stage_off) for v in d.values())
 
 
