@@ -70,6 +70,11 @@ class Plan:
     def first_grad_slot(self) -> int:
         return 2 if self.two_level else 1  # arena slot 0 = replica, slot 1 = partial sum (two-level)
 
+    def arena_elems_of(self, rank: int) -> int:
+        """Size of rank `rank`'s arena (ranks can host different numbers of workers)."""
+        n_local = sum(1 for w in range(self.W) if placement_gpu(w, self.world) == rank)
+        return self.P * (self.first_grad_slot + n_local)
+
     def grad_offset(self, worker: int) -> Tuple[int, int]:
         """(rank, element offset in that rank's arena) of a worker's gradient buffer."""
         r = placement_gpu(worker, self.world)
@@ -177,7 +182,7 @@ class ParameterServer:
         self._s_in, self._s_out = torch.cuda.Stream(), torch.cuda.Stream()
         if world > 1:
             self._exchange_handles()
-            self._flag_ptrs = _ptrs([self.peer_base[r] + 4 * self.plan.arena_elems for r in range(world)])
+            self._flag_ptrs = _ptrs([self.peer_base[r] + 4 * self.plan.arena_elems_of(r) for r in range(world)])
             if transport == "nccl":
                 self._init_nccl()
             import torch.distributed as dist

@@ -111,6 +111,9 @@ def test_plan_layout():
     assert [len(p.launches) for p in p4] == [1, 1, 0, 0]
     with pytest.raises(ValueError):
         b200ps.build_plan(smap, 4, 2, 2)
+    # ranks may host different numbers of workers: every rank must know every arena's size (barrier flags sit behind it)
+    odd = [b200ps.build_plan(smap, 5, r, 2) for r in range(2)]
+    assert [p.arena_elems for p in odd] == [4 * P, 3 * P] and all(p.arena_elems_of(r) == odd[r].arena_elems for p in odd for r in range(2))
     # two-level: one partial sum per GPU is folded, arena gains the partial slot
     t2 = [b200ps.build_plan(smap, 8, r, 2, "two_level") for r in range(2)]
     assert all(p.arena_elems == (2 + 4) * P for p in t2) and t2[0].launches[0].grad_src == [(0, P), (1, P)]
