@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
     ap.add_argument("--barrier", default="peer", choices=["peer", "nccl"], help="cross-rank barrier of a step when N > 1")
+    ap.add_argument("--no-overlap", action="store_true", help="N > 1: fold, barrier, apply in sequence instead of pipelined")
     ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
@@ -402,7 +403,7 @@ def main():
         K.set_dense_tuning(*[int(x) for x in os.environ["B200PS_DENSE_TUNING"].split(",")])
     label, sizes, S, W, opt = workload(args.workload, world)
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
-                                aggregate=args.aggregate, barrier=args.barrier)
+                                aggregate=args.aggregate, barrier=args.barrier, overlap=not args.no_overlap)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
@@ -429,7 +430,7 @@ def main():
     launches0 = K.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    ps.profile = world > 1
+    ps.profile = world > 1 and not ps.overlap
     ev[0].record()
     for i in range(args.steps):
         if world == 1:
@@ -440,7 +441,7 @@ def main():
             ps.step()
     ev[1].record()
     sync()
-    phases = ps.phase_ms() if world > 1 else None
+    phases = ps.phase_ms() if ps.profile else None
     ps.profile = False
     clocks = sampler.finish()
     launches = K.launch_count() - launches0
@@ -521,6 +522,7 @@ def main():
             "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": ps.plan.P,
                        "transport": args.transport if world > 1 else "local",
                        "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
+                       "pipelined": bool(ps.overlap),
                        "l2": "inputs exceed L2 (per step each GPU streams "
                              f"{ps.algorithmic_bytes_per_step() / 1e9:.2f} GB >> 126 MB), no flush needed"},
             "ps_steps_per_sec": round(steps_per_s, 3),

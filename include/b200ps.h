@@ -172,6 +172,13 @@ int b200ps_ipc_close(void* d_ptr);
 #define B200PS_BARRIER_WORDS 16
 int b200ps_peer_barrier(uint32_t* const* d_flags_by_rank, int rank, int world, uint32_t epoch, void* stream);
 int b200ps_peer_barrier_error(const uint32_t* d_my_flags, void* stream);
+/* One-way signals for pipelining a step slice by slice.  signal: after the work queued before it
+ * on `stream` has completed, store `epoch` into one flag word (a peer pointer into the consumer's
+ * arena).  wait: hold `stream` until d_flags[r] >= epoch for every rank r set in rank_mask (words
+ * in local memory; bounded like the barrier, a timeout sets *d_error_word = 1). */
+int b200ps_peer_signal(uint32_t* d_flag, uint32_t epoch, void* stream);
+int b200ps_peer_wait(const uint32_t* d_flags, uint32_t rank_mask, uint32_t epoch, uint32_t* d_error_word,
+                     void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Sparse group: embedding tables sharded by rows (TF "div" partitioning), SURVEY.md 8(a) rows

@@ -78,6 +78,8 @@ SIGNATURES = {
     "b200ps_ipc_close": (_i32, [_vp]),
     "b200ps_peer_barrier": (_i32, [_vp, _i32, _i32, _u32, _vp]),
     "b200ps_peer_barrier_error": (_i32, [_vp, _vp]),
+    "b200ps_peer_signal": (_i32, [_vp, _u32, _vp]),
+    "b200ps_peer_wait": (_i32, [_vp, _u32, _u32, _vp, _vp]),
     "b200ps_sparse_gather": (_i32, [_vp, _vp, C.POINTER(TableGeom), _vp, _u64, _vp]),
     "b200ps_sparse_serve": (_i32, [_vp, _vp, _vp, _i32, _u64, C.POINTER(TableGeom), _vp]),
     "b200ps_sparse_route": (_i32, [_vp, _vp, _u64, C.POINTER(TableGeom), _vp, _vp]),

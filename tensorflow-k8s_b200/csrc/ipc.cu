@@ -118,3 +118,51 @@ extern "C" int b200ps_peer_barrier_error(const uint32_t* d_my_flags, void* strea
     B200PS_REQUIRE(e == 0, B200PS_ERR_STATE, "a peer barrier timed out: some rank never arrived");
     return B200PS_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// One-way signals through peer memory, for pipelining a step slice by slice: a rank that has
+// finished producing slice s (its partial sum) stores the step number into the owner's flag word
+// for (s, rank); the owner's stream waits for the words of all producing ranks before its apply
+// kernel for s starts -- while the producers are already folding the next slices.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+__global__ void peer_signal_kernel(uint32_t* flag, uint32_t epoch) {
+    __threadfence_system();  // the producing kernel has completed; order the flag behind its stores
+    *(volatile uint32_t*)flag = epoch;
+}
+
+__global__ void peer_wait_kernel(const uint32_t* flags, uint32_t rank_mask, uint32_t epoch, uint32_t* error_word) {
+    const int t = threadIdx.x;
+    if ((rank_mask >> t) & 1u) {
+        const volatile uint32_t* f = flags + t;
+        const long long t0 = clock64();
+        while ((int32_t)(*f - epoch) < 0) {
+            if (clock64() - t0 > 8000000000ll) {
+                *error_word = 1u;
+                break;
+            }
+        }
+    }
+    __threadfence_system();
+}
+
+}  // namespace
+
+extern "C" int b200ps_peer_signal(uint32_t* d_flag, uint32_t epoch, void* stream) {
+    B200PS_REQUIRE(d_flag && ((uintptr_t)d_flag & 3) == 0, B200PS_ERR_INVALID, "null or misaligned flag word");
+    peer_signal_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_flag, epoch);
+    B200PS_CUDA(cudaGetLastError());
+    b200ps::g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+extern "C" int b200ps_peer_wait(const uint32_t* d_flags, uint32_t rank_mask, uint32_t epoch, uint32_t* d_error_word,
+                                void* stream) {
+    B200PS_REQUIRE(d_flags && d_error_word, B200PS_ERR_INVALID, "null flag array or error word");
+    if (rank_mask == 0) return B200PS_OK;
+    peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_flags, rank_mask, epoch, d_error_word);
+    B200PS_CUDA(cudaGetLastError());
+    b200ps::g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}

@@ -32,6 +32,9 @@ from .layout import ShardMap
 
 IPC_BYTES = 64
 BARRIER_WORDS = 16  # B200PS_BARRIER_WORDS
+SLICE_FLAG_STRIDE = 16  # words per slice in the slice-ready flags: one per producing rank
+MAX_SLICES = 64
+FLAG_WORDS = BARRIER_WORDS + MAX_SLICES * SLICE_FLAG_STRIDE  # behind every arena
 
 
 # --------------------------------------------------------------------------------------------------
@@ -144,7 +147,7 @@ class ParameterServer:
     def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
                  lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
                  world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20,
-                 aggregate: str = "flat", barrier: str = "peer"):
+                 aggregate: str = "flat", barrier: str = "peer", overlap: bool = True):
         if barrier not in ("peer", "nccl"):
             raise ValueError("barrier must be 'peer' (flags in peer memory) or 'nccl' (a 4-byte all-reduce)")
         if optimizer not in ("sgd", "adam"):
@@ -162,8 +165,9 @@ class ParameterServer:
         self.profile = False  # True: step() brackets its phases with CUDA events (see phase_ms)
         self._events: Dict[str, List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = {"fold": [], "apply": []}
         P = self.plan.P
-        self.arena = Arena(self.plan.arena_elems + BARRIER_WORDS)  # barrier flags live behind the buffers
-        self.barrier_kind, self._epoch = barrier, 0
+        self.arena = Arena(self.plan.arena_elems + FLAG_WORDS)  # barrier + slice-ready flags live behind the buffers
+        self.overlap = overlap and self.plan.two_level and num_shards <= MAX_SLICES
+        self.barrier_kind, self._epoch, self._step_no = barrier, 0, 0
         self.arena.tensor[self.plan.arena_elems:].zero_()
         self.replica = self.arena.tensor[:P]
         g0 = self.plan.first_grad_slot
@@ -287,6 +291,46 @@ class ParameterServer:
             check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr() + o), C.c_void_p(v.data_ptr() + o), g, nbuf, n,
                                               self.inv_w, C.byref(a), mir, len(L.mirror_ranks), self._stream()))
 
+    def _step_overlapped(self, a):
+        """Two-level aggregation pipelined slice by slice over two streams: the fold stream produces
+        this GPU's partial sum of slice 0, 1, 2, ... and signals each slice's owner as soon as it is
+        done; the apply stream of an owner waits for all producers of a slice, then runs the fused
+        apply (NVLink-bound) while the local folds (HBM-bound) of later slices are still running."""
+        cur = torch.cuda.current_stream()
+        self._step_no += 1
+        e, P, S = self._step_no, self.plan.P, self.plan.S
+        self._s_in.wait_stream(cur)   # fold stream
+        self._s_out.wait_stream(cur)  # apply stream
+        flag_base = lambda r: self.peer_base[r] + 4 * (self.plan.arena_elems_of(r) + BARRIER_WORDS)
+        with torch.cuda.stream(self._s_in):
+            if self.plan.local_workers:
+                check(lib.b200ps_set_dense_tuning(256, 8, 2))
+                for s in range(S):
+                    b, en = self.map.slice(s)
+                    if en > b:
+                        bufs = _ptrs([self.grads[w].data_ptr() + 4 * b for w in self.plan.local_workers])
+                        check(lib.b200ps_dense_fold(C.c_void_p(self.partial.data_ptr() + 4 * b), bufs,
+                                                    len(self.plan.local_workers), en - b, self._stream()))
+                    owner = placement_gpu(s, self.world)
+                    check(lib.b200ps_peer_signal(C.c_void_p(flag_base(owner) + 4 * (s * SLICE_FLAG_STRIDE + self.rank)), e,
+                                                 self._stream()))
+        with torch.cuda.stream(self._s_out):
+            # few CTAs: the apply is NVLink-latency-bound and must leave SM slots to the folds
+            check(lib.b200ps_set_dense_tuning(256, 2, 2))
+            err = C.c_void_p(self.arena.ptr + 4 * (self.plan.arena_elems + 9))
+            for L in self.plan.launches:
+                mask = 0
+                for r, _ in L.grad_src:
+                    mask |= 1 << r
+                check(lib.b200ps_peer_wait(C.c_void_p(flag_base(self.rank) + 4 * L.shard * SLICE_FLAG_STRIDE), mask, e, err,
+                                           self._stream()))
+                if L.end > L.begin:
+                    self._launch(L, L.begin, L.end, a)
+            check(lib.b200ps_set_dense_tuning(256, 8, 2))
+        cur.wait_stream(self._s_in)
+        cur.wait_stream(self._s_out)
+        self._barrier()  # every replica holds every updated slice; partial sums may be overwritten
+
     def step(self):
         """push + aggregate + apply + pull for every local shard; gradients are already in the
         workers' device buffers (`grad_buffer`)."""
@@ -294,6 +338,8 @@ class ParameterServer:
         a = self._opt_scalars()
         if self.transport == "nccl" and self.world > 1:
             return self._step_nccl(a)
+        if self.overlap and not self.profile:
+            return self._step_overlapped(a)
         if self.plan.two_level and self.plan.local_workers:
             # local half of the aggregation: one partial sum per GPU, before anything crosses NVLink
             bufs = _ptrs([self.grads[w].data_ptr() for w in self.plan.local_workers])

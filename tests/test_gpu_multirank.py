@@ -66,3 +66,12 @@ def test_two_level_aggregation_is_bit_exact(S, W, opt):
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
     _run(2, S, W, opt, "peer", "two_level")
+
+
+@pytest.mark.parametrize("S,W,opt", [(4, 8, "adam"), (3, 5, "sgd"), (2, 1, "adam")])
+def test_pipelined_two_level_step_is_bit_exact(S, W, opt):
+    """Fold stream + apply stream with per-slice ready flags in peer memory: same bits."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, S, W, opt, "peer", "two_level", "overlap")
