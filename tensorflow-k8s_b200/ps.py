@@ -167,6 +167,10 @@ class ParameterServer:
         P = self.plan.P
         self.arena = Arena(self.plan.arena_elems + FLAG_WORDS)  # barrier + slice-ready flags live behind the buffers
         self.overlap = overlap and self.plan.two_level and num_shards <= MAX_SLICES
+        import os
+
+        geo = os.environ.get("B200PS_OVERLAP_APPLY_GEOMETRY")  # "threads,ctas_per_sm,unroll" -- for experiments
+        self.overlap_apply_geometry = tuple(int(x) for x in geo.split(",")) if geo else (256, 2, 2)
         self.barrier_kind, self._epoch, self._step_no = barrier, 0, 0
         self.arena.tensor[self.plan.arena_elems:].zero_()
         self.replica = self.arena.tensor[:P]
@@ -316,7 +320,7 @@ class ParameterServer:
                                                  self._stream()))
         with torch.cuda.stream(self._s_out):
             # few CTAs: the apply is NVLink-latency-bound and must leave SM slots to the folds
-            check(lib.b200ps_set_dense_tuning(256, 2, 2))
+            check(lib.b200ps_set_dense_tuning(*self.overlap_apply_geometry))
             err = C.c_void_p(self.arena.ptr + 4 * (self.plan.arena_elems + 9))
             for L in self.plan.launches:
                 mask = 0
