@@ -44,9 +44,34 @@ constexpr uint32_t NONE = 0xFFFFFFFFu;
 
 enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_NLONG = 4, HDR_NCHUNKS = 5, HDR_WORDS = 64 };
 
+// Unsigned 32-bit division by a run-time constant without a divide instruction (Granlund &
+// Montgomery): exact for every 32-bit numerator.  A hardware-free u64 divide costs ~100
+// instructions per lane and made the row kernels issue-bound (ncu: issue slots 48 % busy).
+struct FastDiv {
+    uint32_t d, magic, shift;
+    __host__ void set(uint32_t divisor) {
+        d = divisor ? divisor : 1;
+        uint32_t L = 0;
+        while (L < 32 && (1ull << L) < d) ++L;  // ceil(log2 d)
+        if ((1ull << L) == d) {
+            magic = 0;  // power of two: a shift
+            shift = L;
+        } else {
+            magic = (uint32_t)((((1ull << L) - d) << 32) / d + 1);
+            shift = L - 1;
+        }
+    }
+    __device__ __forceinline__ uint32_t div(uint32_t n) const {
+        if (magic == 0) return n >> shift;
+        const uint32_t t = __umulhi(n, magic);
+        return (t + ((n - t) >> 1)) >> shift;
+    }
+};
+
 struct Geom {
-    uint64_t rows;
-    uint64_t q, r, t;  // div partition: q = rows / S, r = rows % S, t = r * (q + 1)
+    uint64_t rows;            // < 2^32
+    uint32_t q, r, t;         // div partition: q = rows / S, r = rows % S, t = r * (q + 1)
+    FastDiv by_q1, by_q, by_world;  // / (q + 1), / q, / world
     int dim, nshards, rank, world;
 };
 
@@ -54,11 +79,13 @@ struct IdSources {
     const int64_t* ids[B200PS_MAX_WORKERS];
     uint32_t per_worker;
     uint32_t n_total;
+    FastDiv by_per_worker;
 };
 
 struct RowSources {
     const float* rows[B200PS_MAX_WORKERS];
     uint32_t per_worker;
+    FastDiv by_per_worker;
 };
 
 struct ShardBases {
@@ -66,16 +93,21 @@ struct ShardBases {
     float* accum[B200PS_MAX_WORKERS];  // row 0 of shard s (Adagrad accumulator) or null
 };
 
-__device__ __forceinline__ int owner_of(const Geom& g, uint64_t id, uint64_t* local_row) {
+// owner shard and row inside it (ids are < rows < 2^32, so 32-bit arithmetic is exact)
+__device__ __forceinline__ int owner_of(const Geom& g, uint64_t id64, uint64_t* local_row) {
+    const uint32_t id = (uint32_t)id64;
     if (id < g.t) {
-        const uint64_t s = id / (g.q + 1);
+        const uint32_t s = g.by_q1.div(id);
         *local_row = id - s * (g.q + 1);
         return (int)s;
     }
-    const uint64_t k = (id - g.t) / g.q;
+    const uint32_t k = g.by_q.div(id - g.t);
     *local_row = (id - g.t) - k * g.q;
     return (int)(g.r + k);
 }
+
+// does shard s live on this GPU?  (shard s -> GPU s mod world)
+__device__ __forceinline__ int gpu_of(const Geom& g, int s) { return s - (int)(g.by_world.div((uint32_t)s) * (uint32_t)g.world); }
 
 // ------------------------------------------------------------------------------------------------
 // workspace
@@ -239,7 +271,7 @@ __device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSource
                                                uint32_t limit, uint32_t* key, uint32_t* val, bool count_bad) {
     if (idx >= limit) return NONE;
     if (MODE == 0) {
-        const uint32_t w = idx / src.per_worker, pos = idx - w * src.per_worker;
+        const uint32_t w = src.by_per_worker.div(idx), pos = idx - w * src.per_worker;
         const int64_t id = src.ids[w][pos];
         *val = idx;
         if (id < 0 || (uint64_t)id >= g.rows) {
@@ -248,7 +280,7 @@ __device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSource
         }
         *key = (uint32_t)id;
         uint64_t lr;
-        return (owner_of(g, (uint64_t)id, &lr) % g.world) == g.rank ? (*key & 255u) : NONE;
+        return gpu_of(g, owner_of(g, (uint64_t)id, &lr)) == g.rank ? (*key & 255u) : NONE;
     }
     *key = a.key_in[idx];
     *val = a.val_in[idx];
@@ -300,23 +332,40 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
         rank[b] = start + __popc(peers & lt);
     }
     __syncthreads();
-    {  // bin t: exclusive offsets over the warps, plus the global base of (bin, this CTA)
-        const int t = threadIdx.x;
-        uint32_t run = a.hist[t * a.nb + blockIdx.x];
+    // Stage the tile in shared memory in (bin, input order) -- its position inside the tile -- and
+    // write it out from there: entries of one bin leave as one contiguous run instead of 32
+    // scattered 4-byte stores per warp instruction (ncu: 30 sectors per store request before).
+    __shared__ uint32_t tile_start[BINS];  // first staged position of each bin
+    __shared__ uint32_t gbase[BINS];       // first global position of (bin, this CTA)
+    __shared__ uint32_t skey[TILE], sval[TILE];
+    __shared__ uint32_t tile_total;
+    {
+        const int t = threadIdx.x;  // one bin per thread: exclusive offsets over the warps
+        uint32_t run = 0;
 #pragma unroll
         for (int k = 0; k < WARPS; ++k) {
             const uint32_t c = cnt[k][t];
             cnt[k][t] = run;
             run += c;
         }
+        gbase[t] = a.hist[t * a.nb + blockIdx.x];
+        tile_start[t] = block_exclusive_scan(run, &tile_total);  // over the 256 bins; total -> shared
     }
     __syncthreads();
 #pragma unroll
     for (int b = 0; b < ITEMS; ++b) {
         if (bin[b] == NONE) continue;
-        const uint32_t dst = cnt[w][bin[b]] + rank[b];
-        a.key_out[dst] = key[b];
-        a.val_out[dst] = val[b];
+        const uint32_t lp = tile_start[bin[b]] + cnt[w][bin[b]] + rank[b];
+        skey[lp] = key[b];
+        sval[lp] = val[b];
+    }
+    __syncthreads();
+    for (uint32_t lp = threadIdx.x; lp < tile_total; lp += TILE_THREADS) {
+        const uint32_t k = skey[lp];
+        const uint32_t bn = (MODE == 0 ? k : (k >> a.shift)) & 255u;
+        const uint32_t dst = gbase[bn] + (lp - tile_start[bn]);
+        a.key_out[dst] = k;
+        a.val_out[dst] = sval[lp];
     }
     if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = *a.total;  // sum of the histogram = #kept
 }
@@ -367,7 +416,7 @@ __device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
 }
 
 __device__ __forceinline__ const float* grad_row(const RowSources& gs, uint32_t entry, int dim) {
-    const uint32_t w = entry / gs.per_worker, pos = entry - w * gs.per_worker;
+    const uint32_t w = gs.by_per_worker.div(entry), pos = entry - w * gs.per_worker;
     return gs.rows[w] + (uint64_t)pos * (uint64_t)dim;
 }
 
@@ -590,9 +639,12 @@ int make_geom(const b200ps_table_geom_t* in, Geom* g) {
     B200PS_REQUIRE(in->world >= 1 && in->rank >= 0 && in->rank < in->world, B200PS_ERR_RANGE, "rank %d of world %d", in->rank,
                    in->world);
     g->rows = in->rows;
-    g->q = in->rows / (uint64_t)in->nshards;
-    g->r = in->rows % (uint64_t)in->nshards;
+    g->q = (uint32_t)(in->rows / (uint64_t)in->nshards);
+    g->r = (uint32_t)(in->rows % (uint64_t)in->nshards);
     g->t = g->r * (g->q + 1);
+    g->by_q1.set(g->q + 1);
+    g->by_q.set(g->q);  // q == 0 only when every id is below t, so the divisor is never used then
+    g->by_world.set((uint32_t)in->world);
     g->dim = in->dim;
     g->nshards = in->nshards;
     g->rank = in->rank;
@@ -636,6 +688,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     if (int rc = fill_bases(geom, d_shard_base, d_accum_base, &tb)) return rc;
     RowSources gs{};
     gs.per_worker = (uint32_t)ids_per_worker;
+    gs.by_per_worker.set(gs.per_worker);
     for (int w = 0; w < W; ++w) {
         B200PS_REQUIRE(d_grad_rows[w] && ((uintptr_t)d_grad_rows[w] & 15) == 0, B200PS_ERR_INVALID,
                        "gradient rows of worker %d must be a 16-byte aligned device pointer", w);
@@ -737,6 +790,7 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
                    workspace_bytes, ws.bytes);
     IdSources src{};
     src.per_worker = (uint32_t)ids_per_worker;
+    src.by_per_worker.set(src.per_worker);
     src.n_total = (uint32_t)n;
     for (int w = 0; w < W; ++w) {
         B200PS_REQUIRE(d_ids[w], B200PS_ERR_INVALID, "ids of worker %d are null", w);
@@ -927,13 +981,13 @@ __global__ void __launch_bounds__(256, 4) sparse_serve_kernel(const __grid_const
             rd[r] = nullptr;
             wr[r] = nullptr;
             if (e < src.n_total) {
-                const uint32_t w = e / src.per_worker, pos = e - w * src.per_worker;
+                const uint32_t w = src.by_per_worker.div(e), pos = e - w * src.per_worker;
                 const int64_t id = src.ids[w][pos];
                 const bool in_range = id >= 0 && (uint64_t)id < g.rows;
                 uint64_t lrow = 0;
                 const int s = in_range ? owner_of(g, (uint64_t)id, &lrow) : 0;
                 // an out-of-range id belongs to nobody: the GPU of shard 0 answers it with zeros
-                if (s % g.world == g.rank) {
+                if (gpu_of(g, s) == g.rank) {
                     wr[r] = reinterpret_cast<float4*>(sa.out[w] + (uint64_t)pos * (uint64_t)g.dim);
                     if (in_range) rd[r] = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
                 }
@@ -973,7 +1027,7 @@ __global__ void __launch_bounds__(256, 4) sparse_route_kernel(const __grid_const
                 const int64_t id = ids[k];
                 if (id >= 0 && (uint64_t)id < g.rows) {
                     uint64_t lrow;
-                    const int o = owner_of(g, (uint64_t)id, &lrow) % g.world;
+                    const int o = gpu_of(g, owner_of(g, (uint64_t)id, &lrow));
                     if (o != g.rank) wr[r] = reinterpret_cast<float4*>(ra.dst[o] + (uint64_t)k * (uint64_t)g.dim);
                 }
             }
@@ -1005,6 +1059,7 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
     ServeArgs sa{};
     IdSources src{};
     src.per_worker = (uint32_t)ids_per_worker;
+    src.by_per_worker.set(src.per_worker);
     src.n_total = (uint32_t)n;
     for (int w = 0; w < W; ++w) {
         B200PS_REQUIRE(d_out[w] && ((uintptr_t)d_out[w] & 15) == 0 && d_ids[w], B200PS_ERR_INVALID,
