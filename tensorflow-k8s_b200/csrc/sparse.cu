@@ -442,16 +442,17 @@ struct ApplyArgs {
 };
 
 // continues the left fold of column c: acc + row[j0] + row[j0+1] + ... (sorted entries [j0, j1) of
-// the plan), eight gradient rows in flight, added strictly in order
+// the plan), F gradient rows in flight, added strictly in order
+template <int F = 8>
 __device__ __forceinline__ float4 fold_rows(float4 acc, const RowSources& gs, const uint32_t* __restrict__ perm, uint32_t j0,
                                             uint32_t j1, int dim, int c) {
     uint32_t j = j0;
-    for (; j + 8 <= j1; j += 8) {
-        float4 r[8];
+    for (; j + F <= j1; j += F) {
+        float4 r[F];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) r[k] = ldg_row4(grad_row(gs, perm[j + k], dim), c);
+        for (int k = 0; k < F; ++k) r[k] = ldg_row4(grad_row(gs, perm[j + k], dim), c);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc = add4(acc, r[k]);
+        for (int k = 0; k < F; ++k) acc = add4(acc, r[k]);
     }
     for (; j < j1; ++j) acc = add4(acc, ldg_row4(grad_row(gs, perm[j], dim), c));
     return acc;
@@ -545,7 +546,7 @@ __global__ void __launch_bounds__(256) long_partials_kernel(const __grid_constan
         const uint32_t j0 = s0 + d.y * SEG_CHUNK, j1 = s1 - j0 < SEG_CHUNK ? s1 : j0 + SEG_CHUNK;
         for (int c = lane; c < dim4; c += LG)
             reinterpret_cast<float4*>(a.partials + (uint64_t)ci * (uint64_t)g.dim)[c] =
-                fold_rows(ldg_row4(grad_row(gs, a.perm[j0], g.dim), c), gs, a.perm, j0 + 1, j1, g.dim, c);
+                fold_rows<16>(ldg_row4(grad_row(gs, a.perm[j0], g.dim), c), gs, a.perm, j0 + 1, j1, g.dim, c);
     }
 }
 
@@ -566,7 +567,15 @@ __global__ void __launch_bounds__(256) long_final_kernel(const __grid_constant__
         for (int c = lane; c < dim4; c += LG) {
             const float4* p = reinterpret_cast<const float4*>(a.partials + (uint64_t)base * (uint64_t)g.dim) + c;
             float4 total = p[0];
-            for (uint32_t j = 1; j < nchunks; ++j) total = add4(total, p[(uint64_t)j * (uint64_t)dim4]);
+            uint32_t j = 1;
+            for (; j + 8 <= nchunks; j += 8) {  // eight partial rows in flight, added in chunk order
+                float4 r[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) r[k] = p[(uint64_t)(j + k) * (uint64_t)dim4];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) total = add4(total, r[k]);
+            }
+            for (; j < nchunks; ++j) total = add4(total, p[(uint64_t)j * (uint64_t)dim4]);
             update_row<ADAGRAD>(row, arow, c, total, a.inv_w, a.lr);
         }
     }
@@ -968,7 +977,7 @@ __global__ void __launch_bounds__(256, 4) sparse_serve_kernel(const __grid_const
                                                            const __grid_constant__ ShardBases tb,
                                                            const __grid_constant__ IdSources src,
                                                            const __grid_constant__ Geom g) {
-    constexpr int R = 4;
+    constexpr int R = 8;  // rows in flight per lane group
     const int lane = threadIdx.x % LG;
     const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
     const int dim4 = g.dim / 4;
