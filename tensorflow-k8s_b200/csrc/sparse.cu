@@ -977,7 +977,7 @@ __global__ void __launch_bounds__(256, 4) sparse_serve_kernel(const __grid_const
                                                            const __grid_constant__ ShardBases tb,
                                                            const __grid_constant__ IdSources src,
                                                            const __grid_constant__ Geom g) {
-    constexpr int R = 8;  // rows in flight per lane group
+    constexpr int R = 4;  // rows in flight per lane group (8 spills under the 64-register cap and is slower)
     const int lane = threadIdx.x % LG;
     const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
     const int dim4 = g.dim / 4;
