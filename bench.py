@@ -473,6 +473,22 @@ def main():
                     "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
                     "launches_per_step": n_kernels_step, "phases_ms": {k: round(v, 4) for k, v in phases.items()}}
 
+    if roofline is None and world > 1:
+        # pipelined multi-GPU step: the exchange is the bound.  Per step a GPU receives the partial
+        # sums (or gradients) of its slices from the other GPUs plus every other owner's updated
+        # slices into its replica, all on the inbound direction of its NVLink ports.
+        mine = sum(L.end - L.begin for L in ps.plan.launches)
+        inbound = 4 * (sum((L.end - L.begin) * sum(1 for r, _ in L.grad_src if r != rank) for L in ps.plan.launches)
+                       + (ps.plan.P - mine))
+        inbound = reduce_max(float(inbound))
+        ach = inbound / ms_step / 1e6
+        roofline = {"bound": "nvlink", "achieved": round(ach, 1), "peak": 770.0, "unit": "GB/s", "frac": round(ach / 770.0, 4),
+                    "traffic": None, "kernel": kname + " + dense_fold, pipelined over two streams",
+                    "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); 900 nominal",
+                    "inbound_bytes_per_gpu_per_step": int(inbound),
+                    "note": "N > 1: peer loads (push) and peer stores (pull) share each link direction, so the step is "
+                            "NVLink-bound; achieved = inbound bytes / whole step time (folds and barrier included)"}
+
     # ---- end to end with HOST buffers ----
     e2e = None
     if not args.no_e2e:
