@@ -162,6 +162,7 @@ class ParameterServer:
         self.rank, self.world, self.group, self.transport = rank, world, group, transport
         self.chunk = max(1024, chunk_elems // 1024 * 1024)
         self.t = 0
+        self.trace = None  # a list: the pipelined step appends (label, event) pairs (tools/overlap_timeline.py)
         self.profile = False  # True: step() brackets its phases with CUDA events (see phase_ms)
         self._events: Dict[str, List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = {"fold": [], "apply": []}
         P = self.plan.P
@@ -303,6 +304,15 @@ class ParameterServer:
         cur = torch.cuda.current_stream()
         self._step_no += 1
         e, P, S = self._step_no, self.plan.P, self.plan.S
+        trace = self.trace  # None, or a list that receives (label, event) pairs of this step
+
+        def tick(label):
+            if trace is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                trace.append((label, ev))
+
+        tick("start")
         self._s_in.wait_stream(cur)   # fold stream
         self._s_out.wait_stream(cur)  # apply stream
         flag_base = lambda r: self.peer_base[r] + 4 * (self.plan.arena_elems_of(r) + BARRIER_WORDS)
@@ -318,6 +328,7 @@ class ParameterServer:
                     owner = placement_gpu(s, self.world)
                     check(lib.b200ps_peer_signal(C.c_void_p(flag_base(owner) + 4 * (s * SLICE_FLAG_STRIDE + self.rank)), e,
                                                  self._stream()))
+                    tick(f"fold+signal {s}")
         with torch.cuda.stream(self._s_out):
             # few CTAs: the apply is NVLink-latency-bound and must leave SM slots to the folds
             check(lib.b200ps_set_dense_tuning(*self.overlap_apply_geometry))
@@ -328,12 +339,16 @@ class ParameterServer:
                     mask |= 1 << r
                 check(lib.b200ps_peer_wait(C.c_void_p(flag_base(self.rank) + 4 * L.shard * SLICE_FLAG_STRIDE), mask, e, err,
                                            self._stream()))
+                tick(f"wait {L.shard}")
                 if L.end > L.begin:
                     self._launch(L, L.begin, L.end, a)
+                tick(f"apply {L.shard}")
             check(lib.b200ps_set_dense_tuning(256, 8, 2))
         cur.wait_stream(self._s_in)
         cur.wait_stream(self._s_out)
+        tick("joined")
         self._barrier()  # every replica holds every updated slice; partial sums may be overwritten
+        tick("barrier")
 
     def step(self):
         """push + aggregate + apply + pull for every local shard; gradients are already in the
