@@ -40,8 +40,10 @@ def parse():
     ap.add_argument("--ids", default="zipf", choices=["zipf", "uniform"], help="id distribution of --workload c2")
     ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
-    ap.add_argument("--barrier", default="peer", choices=["peer", "nccl"], help="cross-rank barrier of a step when N > 1")
-    ap.add_argument("--no-overlap", action="store_true", help="N > 1: fold, barrier, apply in sequence instead of pipelined")
+    ap.add_argument("--barrier", default="nccl", choices=["peer", "nccl"],
+                    help="cross-rank barrier of a step when N > 1: a 4-byte NCCL all-reduce, or flags in peer memory")
+    ap.add_argument("--overlap", action="store_true",
+                    help="N > 1: pipeline the local folds with the NVLink exchange over two streams (helps at N=2, not at N=8)")
     ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
@@ -403,7 +405,7 @@ def main():
         K.set_dense_tuning(*[int(x) for x in os.environ["B200PS_DENSE_TUNING"].split(",")])
     label, sizes, S, W, opt = workload(args.workload, world)
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
-                                aggregate=args.aggregate, barrier=args.barrier, overlap=not args.no_overlap)
+                                aggregate=args.aggregate, barrier=args.barrier, overlap=args.overlap)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)

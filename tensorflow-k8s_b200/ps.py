@@ -147,7 +147,7 @@ class ParameterServer:
     def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
                  lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
                  world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20,
-                 aggregate: str = "flat", barrier: str = "peer", overlap: bool = True):
+                 aggregate: str = "flat", barrier: str = "nccl", overlap: bool = False):
         if barrier not in ("peer", "nccl"):
             raise ValueError("barrier must be 'peer' (flags in peer memory) or 'nccl' (a 4-byte all-reduce)")
         if optimizer not in ("sgd", "adam"):

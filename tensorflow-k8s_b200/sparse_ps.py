@@ -90,7 +90,7 @@ class TableLayout:
 class EmbeddingTable:
     def __init__(self, rows: int, dim: int, num_shards: int, num_workers: int, ids_per_worker: int,
                  optimizer: str = "sgd", lr: float = 0.05, rank: int = 0, world: int = 1, group=None,
-                 accum_init: float = 0.1, barrier: str = "peer"):
+                 accum_init: float = 0.1, barrier: str = "nccl"):
         if barrier not in ("peer", "nccl"):
             raise ValueError("barrier must be 'peer' or 'nccl'")
         if optimizer not in ("sgd", "adagrad"):

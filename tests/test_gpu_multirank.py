@@ -74,4 +74,12 @@ def test_pipelined_two_level_step_is_bit_exact(S, W, opt):
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
-    _run(2, S, W, opt, "peer", "two_level", "overlap")
+    _run(2, S, W, opt, "peer", "two_level", "overlap", "peer")
+
+
+def test_peer_memory_barrier():
+    """The flag barrier through peer memory instead of the NCCL all-reduce: same bits, uneven arenas included."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, 3, 5, "adam", "peer", "flat", "sequential", "peer")
