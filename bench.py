@@ -48,6 +48,7 @@ def parse():
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="SGD workloads on one GPU: launch every step instead of replaying a CUDA graph")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps, capped at 30")
     return ap.parse_args()
@@ -424,8 +425,12 @@ def main():
         return float(t.item())
 
     # ---- device-resident timing: `value` and the roofline ----
+    do_step = ps.step
+    graphed = world == 1 and opt == "sgd" and not args.no_graph
+    if graphed:  # launch-bound workload (C0): replay the step's launches as one CUDA graph
+        do_step = ps.capture_step().replay
     for _ in range(max(args.warmup, 3)):
-        ps.step()
+        do_step()
     sync()
     sampler = ClockSampler(local)
     sampler.start()
@@ -437,10 +442,10 @@ def main():
     for i in range(args.steps):
         if world == 1:
             kev[i][0].record()
-            ps.step()
+            do_step()
             kev[i][1].record()
         else:
-            ps.step()
+            do_step()
     ev[1].record()
     sync()
     phases = ps.phase_ms() if ps.profile else None
@@ -540,7 +545,7 @@ def main():
             "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": ps.plan.P,
                        "transport": args.transport if world > 1 else "local",
                        "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
-                       "pipelined": bool(ps.overlap),
+                       "pipelined": bool(ps.overlap), "cuda_graph": bool(graphed),
                        "l2": "inputs exceed L2 (per step each GPU streams "
                              f"{ps.algorithmic_bytes_per_step() / 1e9:.2f} GB >> 126 MB), no flush needed"},
             "ps_steps_per_sec": round(steps_per_s, 3),

@@ -374,6 +374,21 @@ class ParameterServer:
         self._mark("apply", e0)
         self._barrier()  # every replica holds every updated slice
 
+    def capture_step(self) -> "torch.cuda.CUDAGraph":
+        """The launches of one step as a CUDA graph (replay it instead of calling step()).  For the
+        launch-bound end of the size range (BASELINE configs[0], the small end of configs[4]): a
+        1 M-parameter step is ~3 us of kernel time behind ~25 us of host-side launch work.  SGD on
+        one GPU only: Adam's bias-corrected step size is a launch parameter that changes every
+        step, and the cross-rank barriers are not captured."""
+        if self.optimizer != "sgd" or self.world != 1:
+            raise ValueError("capture_step supports SGD on one GPU")
+        self.step()  # warm up outside the capture
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step()
+        return g
+
     def _mark(self, phase: Optional[str] = None, start=None):
         if not self.profile:
             return None

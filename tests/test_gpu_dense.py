@@ -183,3 +183,54 @@ def test_launch_counter_counts():
     K.dense_apply_sgd(p, [p], 0.1)
     K.fill_uniform(p, 1, 1, 1)
     assert K.launch_count() == before + 2
+
+
+def test_parameter_server_host_api_and_graph_replay(oracle):
+    """b200ps.ParameterServer on one GPU (C0 shape: 1 PS + 2 workers, SGD): step(), a captured
+    CUDA-graph replay of it, and step_host() with pinned host buffers all match the oracle bit for bit."""
+    n, W = 1_000_000, 2
+    ps = b200ps.ParameterServer([n], 1, W, optimizer="sgd", lr=0.05)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp = oracle.fill_uniform(P, 1, 0, 0, threads=4)
+    hg = [oracle.fill_uniform(P, 2, 1, w, threads=4) for w in range(W)]
+    for w in range(W):
+        K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
+    ps.step()
+    oracle.dense_sgd(hp, hg, 0.05, threads=4)
+    g = ps.capture_step()          # runs one warm-up step, then records one (recording does not execute)
+    oracle.dense_sgd(hp, hg, 0.05, threads=4)
+    torch.cuda.synchronize()
+    g.replay()
+    oracle.dense_sgd(hp, hg, 0.05, threads=4)
+    torch.cuda.synchronize()
+    assert same(ps.replica, hp)
+    host_g = {w: torch.from_numpy(hg[w]).pin_memory() for w in range(W)}
+    host_o = {0: torch.empty(P, dtype=torch.float32).pin_memory()}
+    ps.step_host(host_g, host_o)
+    torch.cuda.synchronize()
+    oracle.dense_sgd(hp, hg, 0.05, threads=4)
+    assert same(ps.replica, hp) and np.array_equal(host_o[0].numpy().view(np.uint32), hp.view(np.uint32))
+    ps.close()
+
+
+def test_parameter_server_adam_two_shards(oracle):
+    sizes, S, W = [300_000, 77, 50_000], 2, 4
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer="adam", lr=1e-3)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp = oracle.fill_uniform(P, 1, 0, 0)
+    hm, hv = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    for t in (1, 2, 3):
+        hg = [oracle.fill_uniform(P, 2, t, w) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(ps.grad_buffer(w), 2, t, w)
+        ps.step()
+        oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t))
+    d = ps.dump()
+    for s, x in d.items():
+        b, e = x["range"]
+        assert same(torch.from_numpy(x["p"]), hp[b:e]) and same(torch.from_numpy(x["m"]), hm[b:e]) and same(torch.from_numpy(x["v"]), hv[b:e])
+    with pytest.raises(ValueError):
+        ps.capture_step()  # Adam: the step size changes every step
+    ps.close()
