@@ -546,8 +546,10 @@ def main():
                        "transport": args.transport if world > 1 else "local",
                        "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
                        "pipelined": bool(ps.overlap), "cuda_graph": bool(graphed),
-                       "l2": "inputs exceed L2 (per step each GPU streams "
-                             f"{ps.algorithmic_bytes_per_step() / 1e9:.2f} GB >> 126 MB), no flush needed"},
+                       "l2": (f"inputs exceed L2 (per step each GPU streams {ps.algorithmic_bytes_per_step() / 1e9:.2f} GB "
+                              ">> 126 MB), no flush needed") if ps.algorithmic_bytes_per_step() > (512 << 20) else
+                             (f"working set ({ps.algorithmic_bytes_per_step() / 1e6:.0f} MB per step) fits the 126 MB L2 and is "
+                              "NOT flushed between steps: an L2-resident, launch-bound figure, not an HBM one")},
             "ps_steps_per_sec": round(steps_per_s, 3),
             "algorithmic_GBps_per_gpu": round(ps.algorithmic_bytes_per_step() / ms_step / 1e6, 1),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
