@@ -144,7 +144,7 @@ def cpu_run(label, sizes, S, W, opt, steps, warmup, seconds=None):
 
     from oracle import c_oracle as O, np_oracle
 
-    nt = O.max_threads()
+    nt = O.use_all_cores()
     P, _, slices = np_oracle.shard_map(sizes, S, 1024)
     p = O.fill_uniform(P, 1, 0, 0, threads=nt)
     m, v = np.zeros(P, np.float32), np.zeros(P, np.float32)
@@ -201,7 +201,7 @@ C2 = dict(dim=64, S=8, W=8, B=262_144, lr=0.05)
 def ncores():
     from oracle import c_oracle as O
 
-    return O.max_threads()
+    return O.use_all_cores()
 
 
 def sparse_cpu(rows, ids_kind, steps, seconds):
@@ -213,8 +213,9 @@ def sparse_cpu(rows, ids_kind, steps, seconds):
     from oracle import c_oracle as O
 
     dim, W, B = C2["dim"], C2["W"], C2["B"]
-    table = O.fill_uniform(rows * dim, 1, 0, 0, threads=O.max_threads()).reshape(rows, dim)
-    grad = O.fill_uniform(W * B * dim, 2, 1, 0, threads=O.max_threads()).reshape(W * B, dim)
+    nt = O.use_all_cores()
+    table = O.fill_uniform(rows * dim, 1, 0, 0, threads=nt).reshape(rows, dim)
+    grad = O.fill_uniform(W * B * dim, 2, 1, 0, threads=nt).reshape(W * B, dim)
     ids = synth.make_ids(ids_kind, rows, W, B, 1)
     t0, done = time.perf_counter(), 0
     while done < steps:

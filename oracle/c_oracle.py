@@ -57,6 +57,7 @@ def lib():
         L.ps_sparse_apply_sgd.argtypes = [vp, i32, C.c_int64, vp, vp, vp, vp, u64, f32, f32]
         L.ps_sparse_apply_adagrad.argtypes = [vp, vp, i32, C.c_int64, vp, vp, vp, vp, u64, f32, f32]
         L.ps_oracle_max_threads.restype = i32
+        L.ps_oracle_set_threads.argtypes = [i32]
         _lib = L
     return _lib
 
@@ -68,6 +69,13 @@ def _p(a: np.ndarray):
 
 def max_threads() -> int:
     return int(lib().ps_oracle_max_threads())
+
+
+def use_all_cores() -> int:
+    """Use every core this process may run on, whatever OMP_NUM_THREADS says (torchrun exports 1)."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().ps_oracle_set_threads(n)
+    return n
 
 
 def fill_uniform(n, seed, step, worker, first=0, threads=1) -> np.ndarray:

@@ -16,6 +16,14 @@
 #include <omp.h>
 #endif
 
+void ps_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n); /* launchers such as torchrun export OMP_NUM_THREADS=1 */
+#else
+    (void)n;
+#endif
+}
+
 int ps_oracle_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -87,6 +87,7 @@ void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_ba
                              uint64_t n_unique, float inv_w, float lr);
 
 int ps_oracle_max_threads(void);
+void ps_oracle_set_threads(int n); /* overrides OMP_NUM_THREADS for the calls that follow */
 
 #ifdef __cplusplus
 }
