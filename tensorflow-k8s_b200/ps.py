@@ -484,6 +484,46 @@ class ParameterServer:
             out[L.shard] = d
         return out
 
+    # ---- checkpoint / resume ("storage" is a stated goal, k8s-operator.md:2) ----
+    def save(self, directory: str):
+        """Writes this rank's shards -- parameters, optimizer state, step counter -- with the shard
+        map as header: <directory>/ps-rank<r>-of-<G>.npz.  Every rank calls it."""
+        import json
+        import os
+
+        os.makedirs(directory, exist_ok=True)
+        d = self.dump()
+        header = {"format": "b200ps-dense-1", "P_pad": self.plan.P, "shards": self.plan.S, "workers": self.plan.W,
+                  "optimizer": self.optimizer, "t": self.t, "rank": self.rank, "world": self.world,
+                  "slices": {str(s): list(x["range"]) for s, x in d.items()}}
+        arrays = {"header": np.frombuffer(json.dumps(header).encode(), dtype=np.uint8)}
+        for s, x in d.items():
+            for k in ("p", "m", "v"):
+                if k in x:
+                    arrays[f"{k}{s}"] = x[k]
+        np.savez(os.path.join(directory, f"ps-rank{self.rank}-of-{self.world}.npz"), **arrays)
+
+    def load(self, directory: str):
+        """Restores a job saved with the same shard map and world size: every rank reads every
+        rank's parameters (its replica holds all slices) and its own optimizer state."""
+        import json
+        import os
+
+        for r in range(self.world):
+            z = np.load(os.path.join(directory, f"ps-rank{r}-of-{self.world}.npz"))
+            h = json.loads(bytes(z["header"]).decode())
+            if (h["P_pad"], h["shards"], h["optimizer"], h["world"]) != (self.plan.P, self.plan.S, self.optimizer, self.world):
+                raise ValueError(f"checkpoint of rank {r} was written for a different job layout: {h}")
+            for s, (b, e) in h["slices"].items():
+                self.replica[b:e].copy_(torch.from_numpy(z[f"p{s}"]))
+                if r == self.rank and int(s) in self.state:
+                    m, v = self.state[int(s)]
+                    m.copy_(torch.from_numpy(z[f"m{s}"]))
+                    v.copy_(torch.from_numpy(z[f"v{s}"]))
+            if r == self.rank:
+                self.t = int(h["t"])
+        torch.cuda.synchronize()
+
     def algorithmic_bytes_per_step(self) -> int:
         """(4W + 8) n for SGD, (4W + 24) n for Adam, summed over local slices.
         (Two-level aggregation moves more local bytes -- the partial sum is written and re-read --

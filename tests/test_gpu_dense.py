@@ -234,3 +234,38 @@ def test_parameter_server_adam_two_shards(oracle):
     with pytest.raises(ValueError):
         ps.capture_step()  # Adam: the step size changes every step
     ps.close()
+
+
+def test_checkpoint_resume_continues_bit_exactly(tmp_path):
+    """save -> new ParameterServer -> load -> keep training gives the bits of never having stopped
+    (parameters, m, v and the Adam step counter all travel)."""
+    sizes, S, W = [40_000, 123, 9_000], 2, 3
+
+    def grads(ps, t):
+        for w in range(W):
+            K.fill_uniform(ps.grad_buffer(w), 2, t, w)
+
+    a = b200ps.ParameterServer(sizes, S, W, optimizer="adam")
+    a.init_uniform(1)
+    for t in (1, 2):
+        grads(a, t)
+        a.step()
+    a.save(str(tmp_path))
+    for t in (3, 4):
+        grads(a, t)
+        a.step()
+    b = b200ps.ParameterServer(sizes, S, W, optimizer="adam")
+    b.load(str(tmp_path))
+    assert b.t == 2
+    for t in (3, 4):
+        grads(b, t)
+        b.step()
+    da, db = a.dump(), b.dump()
+    for s in da:
+        for k in ("p", "m", "v"):
+            assert np.array_equal(da[s][k].view(np.uint32), db[s][k].view(np.uint32))
+    c = b200ps.ParameterServer(sizes, 1, W, optimizer="adam")
+    with pytest.raises((ValueError, FileNotFoundError)):
+        c.load(str(tmp_path))  # a different shard map is refused
+    for x in (a, b, c):
+        x.close()
