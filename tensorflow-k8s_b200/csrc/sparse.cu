@@ -972,44 +972,67 @@ struct ServeArgs {
     float* out[B200PS_MAX_WORKERS];  // worker w's pulled rows [B, dim]
 };
 
-template <int LG>
-__global__ void __launch_bounds__(256, 4) sparse_serve_kernel(const __grid_constant__ ServeArgs sa,
-                                                           const __grid_constant__ ShardBases tb,
-                                                           const __grid_constant__ IdSources src,
-                                                           const __grid_constant__ Geom g) {
-    constexpr int R = 4;  // rows in flight per lane group (8 spills under the 64-register cap and is slower)
-    const int lane = threadIdx.x % LG;
-    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
-    const int dim4 = g.dim / 4;
-    for (uint32_t e0 = group; e0 < src.n_total; e0 += R * ngroups) {
+// Copies the rows described in shared memory: entry k of the tile goes from s_src[k] to s_dst[k]
+// (null dst: not this GPU's business; null src with a dst: an out-of-range id, answered with zeros).
+// One lane group per row, R rows in flight per group.
+template <int LG, int R>
+__device__ __forceinline__ void copy_tile_rows(const float4* const* s_src, float4* const* s_dst, int count, int dim4) {
+    constexpr int GROUPS = 256 / LG;
+    const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
+    for (int r0 = grp; r0 < count; r0 += GROUPS * R) {
         const float4* rd[R];
         float4* wr[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const uint32_t e = e0 + r * ngroups;
-            rd[r] = nullptr;
-            wr[r] = nullptr;
-            if (e < src.n_total) {
-                const uint32_t w = src.by_per_worker.div(e), pos = e - w * src.per_worker;
-                const int64_t id = src.ids[w][pos];
-                const bool in_range = id >= 0 && (uint64_t)id < g.rows;
-                uint64_t lrow = 0;
-                const int s = in_range ? owner_of(g, (uint64_t)id, &lrow) : 0;
-                // an out-of-range id belongs to nobody: the GPU of shard 0 answers it with zeros
-                if (gpu_of(g, s) == g.rank) {
-                    wr[r] = reinterpret_cast<float4*>(sa.out[w] + (uint64_t)pos * (uint64_t)g.dim);
-                    if (in_range) rd[r] = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
-                }
-            }
+        for (int k = 0; k < R; ++k) {
+            const int r = r0 + k * GROUPS;
+            rd[k] = r < count ? s_src[r] : nullptr;
+            wr[k] = r < count ? s_dst[r] : nullptr;
         }
         for (int c = lane; c < dim4; c += LG) {
             float4 v[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) v[r] = rd[r] ? rd[r][c] : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < R; ++k) v[k] = rd[k] ? rd[k][c] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                if (wr[r]) wr[r][c] = v[r];
+            for (int k = 0; k < R; ++k)
+                if (wr[k]) wr[k][c] = v[k];
         }
+    }
+}
+
+// Two phases per tile of 256 entries.  A: one THREAD per entry reads its id (coalesced), does the
+// owner / worker arithmetic once and leaves a (source row, destination row) pair in shared memory.
+// B: one LANE GROUP per row copies it.  (The first version did the arithmetic in every lane of the
+// group: ncu showed 42 % of the issue slots busy with it.)
+template <int LG>
+__global__ void __launch_bounds__(256) sparse_serve_kernel(const __grid_constant__ ServeArgs sa,
+                                                           const __grid_constant__ ShardBases tb,
+                                                           const __grid_constant__ IdSources src,
+                                                           const __grid_constant__ Geom g) {
+    __shared__ const float4* s_src[256];
+    __shared__ float4* s_dst[256];
+    const int dim4 = g.dim / 4;
+    for (uint32_t base = blockIdx.x * 256u; base < src.n_total; base += gridDim.x * 256u) {
+        const uint32_t e = base + threadIdx.x;
+        const float4* rd = nullptr;
+        float4* wr = nullptr;
+        if (e < src.n_total) {
+            const uint32_t w = src.by_per_worker.div(e), pos = e - w * src.per_worker;
+            const int64_t id = src.ids[w][pos];
+            const bool in_range = id >= 0 && (uint64_t)id < g.rows;
+            uint64_t lrow = 0;
+            const int s = in_range ? owner_of(g, (uint64_t)id, &lrow) : 0;
+            // an out-of-range id belongs to nobody: the GPU of shard 0 answers it with zeros
+            if (gpu_of(g, s) == g.rank) {
+                wr = reinterpret_cast<float4*>(sa.out[w] + (uint64_t)pos * (uint64_t)g.dim);
+                if (in_range) rd = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
+            }
+        }
+        s_src[threadIdx.x] = rd;
+        s_dst[threadIdx.x] = wr;
+        __syncthreads();
+        const uint32_t left = src.n_total - base;
+        copy_tile_rows<LG, 4>(s_src, s_dst, left < 256u ? (int)left : 256, dim4);
+        __syncthreads();
     }
 }
 
@@ -1089,8 +1112,9 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
     const uint64_t want = (n * (uint64_t)lg + 255) / 256;
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
+    const uint64_t tiles = (n + 255) / 256;
 #define LAUNCH_SERVE(LG) \
-    sparse_serve_kernel<LG><<<resident_grid(sparse_serve_kernel<LG>, 256, want), 256, 0, st>>>(sa, tb, src, g)
+    sparse_serve_kernel<LG><<<resident_grid(sparse_serve_kernel<LG>, 256, tiles), 256, 0, st>>>(sa, tb, src, g)
     switch (lg) {
         case 4: LAUNCH_SERVE(4); break;
         case 8: LAUNCH_SERVE(8); break;
