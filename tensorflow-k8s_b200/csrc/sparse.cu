@@ -474,62 +474,76 @@ __device__ __forceinline__ void update_row(float* row, float* arow, int c, const
 // Segments of at most SEG_CHUNK entries: fold and update here.  Longer ones (hot ids) are only
 // registered -- their chunks are folded by all lane groups of long_partials_kernel and finished by
 // long_final_kernel, in the chunk order the oracle defines.
+//
+// Two phases per tile of 256 unique ids (like sparse_serve_kernel).  A: one THREAD per unique id
+// reads its segment bounds and id (coalesced), resolves the table row once and leaves a descriptor
+// in shared memory.  B: one LANE GROUP per unique id issues the table-row load, folds the segment's
+// gradient rows in order and writes the row back.
 template <int LG, bool ADAGRAD>
 __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant__ ShardBases tb,
                                                            const __grid_constant__ RowSources gs,
                                                            const __grid_constant__ Geom g,
                                                            const __grid_constant__ ApplyArgs a) {
+    constexpr int GROUPS = 256 / LG;
+    __shared__ float* s_row[256];
+    __shared__ float* s_arow[ADAGRAD ? 256 : 1];
+    __shared__ uint32_t s_s0[256], s_len[256], s_base[256];
     const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
-    const int lane = threadIdx.x % LG;
-    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
     const int dim4 = g.dim / 4;
-    // the metadata of the next unique id is fetched while the rows of this one are in flight
-    uint32_t u = group;
-    uint32_t s0 = 0, s1 = 0, id = 0, first = 0;
-    if (u < n_unique) {
-        s0 = a.seg_off[u];
-        s1 = a.seg_off[u + 1];
-        id = a.unique[u];
-        first = a.perm[s0];
-    }
-    while (u < n_unique) {
-        const uint32_t un = u + ngroups;
-        uint32_t n0 = 0, n1 = 0, nid = 0, nfirst = 0;
-        if (un < n_unique) {
-            n0 = a.seg_off[un];
-            n1 = a.seg_off[un + 1];
-            nid = a.unique[un];
-            nfirst = a.perm[n0];
-        }
-        const uint32_t len = s1 - s0;
-        if (len > SEG_CHUNK) {
-            const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK;
-            uint32_t base = 0;
-            if (lane == 0) {
-                const uint32_t idx = atomicAdd(&a.hdr[HDR_NLONG], 1u);
-                base = atomicAdd(&a.hdr[HDR_NCHUNKS], nchunks);
-                a.long_u[idx] = u;
-                a.long_base[idx] = base;
+    for (uint32_t base_u = blockIdx.x * 256u; base_u < n_unique; base_u += gridDim.x * 256u) {
+        {  // phase A
+            const uint32_t u = base_u + threadIdx.x;
+            uint32_t s0 = 0, len = 0, cbase = 0;
+            float* row = nullptr;
+            if (u < n_unique) {
+                s0 = a.seg_off[u];
+                len = a.seg_off[u + 1] - s0;
+                uint64_t lrow;
+                const int s = owner_of(g, a.unique[u], &lrow);
+                row = tb.base[s] + lrow * (uint64_t)g.dim;
+                if (ADAGRAD) s_arow[threadIdx.x] = tb.accum[s] + lrow * (uint64_t)g.dim;
+                if (len > SEG_CHUNK) {
+                    const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK;
+                    const uint32_t idx = atomicAdd(&a.hdr[HDR_NLONG], 1u);
+                    cbase = atomicAdd(&a.hdr[HDR_NCHUNKS], nchunks);
+                    a.long_u[idx] = u;
+                    a.long_base[idx] = cbase;
+                }
             }
-            const int g0 = (threadIdx.x & 31) / LG * LG;  // first lane of this group inside the warp
-            base = __shfl_sync(LG == 32 ? 0xffffffffu : (((1u << LG) - 1u) << g0), base, g0);
-            for (uint32_t j = lane; j < nchunks; j += LG) a.chunks[base + j] = make_uint2(u, j);
-        } else {
-            uint64_t lrow;
-            const int s = owner_of(g, id, &lrow);
-            float* row = tb.base[s] + lrow * (uint64_t)g.dim;
-            float* arow = ADAGRAD ? tb.accum[s] + lrow * (uint64_t)g.dim : nullptr;
+            s_row[threadIdx.x] = row;
+            s_s0[threadIdx.x] = s0;
+            s_len[threadIdx.x] = len;
+            s_base[threadIdx.x] = cbase;
+        }
+        __syncthreads();
+        const uint32_t left = n_unique - base_u;
+        const int count = left < 256u ? (int)left : 256;
+        for (int r = grp; r < count; r += GROUPS) {  // phase B
+            const uint32_t s0 = s_s0[r], len = s_len[r];
+            if (len > SEG_CHUNK) {
+                const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK, cbase = s_base[r];
+                for (uint32_t jj = lane; jj < nchunks; jj += LG) a.chunks[cbase + jj] = make_uint2(base_u + r, jj);
+                continue;
+            }
+            float* row = s_row[r];
+            float* arow = ADAGRAD ? s_arow[r] : nullptr;
             for (int c = lane; c < dim4; c += LG) {
-                float4 acc = ldg_row4(grad_row(gs, first, g.dim), c);
-                acc = fold_rows(acc, gs, a.perm, s0 + 1, s1, g.dim, c);
-                update_row<ADAGRAD>(row, arow, c, acc, a.inv_w, a.lr);
+                // the row being updated does not depend on the fold: get it in flight first
+                float4 rv = reinterpret_cast<const float4*>(row)[c];
+                float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ADAGRAD) ac = reinterpret_cast<const float4*>(arow)[c];
+                float4 acc = ldg_row4(grad_row(gs, a.perm[s0], g.dim), c);
+                acc = fold_rows(acc, gs, a.perm, s0 + 1, s0 + len, g.dim, c);
+                rv.x = upd1<ADAGRAD>(acc.x, rv.x, ac.x, a.inv_w, a.lr);
+                rv.y = upd1<ADAGRAD>(acc.y, rv.y, ac.y, a.inv_w, a.lr);
+                rv.z = upd1<ADAGRAD>(acc.z, rv.z, ac.z, a.inv_w, a.lr);
+                rv.w = upd1<ADAGRAD>(acc.w, rv.w, ac.w, a.inv_w, a.lr);
+                reinterpret_cast<float4*>(row)[c] = rv;
+                if (ADAGRAD) reinterpret_cast<float4*>(arow)[c] = ac;
             }
         }
-        u = un;
-        s0 = n0;
-        s1 = n1;
-        id = nid;
-        first = nfirst;
+        __syncthreads();
     }
 }
 
@@ -725,7 +739,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     // the long-segment counters belong to this apply (a plan may be applied more than once)
     B200PS_CUDA(cudaMemsetAsync(ws.hdr + HDR_NLONG, 0, 2 * sizeof(uint32_t), st));
 #define LAUNCH_APPLY(LG)                                                      \
-    sparse_apply_kernel<LG, ADAGRAD><<<resident_grid(sparse_apply_kernel<LG, ADAGRAD>, 256, want), 256, 0, st>>>(tb, gs, g, a); \
+    sparse_apply_kernel<LG, ADAGRAD><<<resident_grid(sparse_apply_kernel<LG, ADAGRAD>, 256, (n + 255) / 256), 256, 0, st>>>(tb, gs, g, a); \
     long_partials_kernel<LG><<<resident_grid(long_partials_kernel<LG>, 256, want), 256, 0, st>>>(gs, g, a);              \
     long_final_kernel<LG, ADAGRAD><<<sms, 256, 0, st>>>(tb, g, a)
     switch (lg) {
@@ -1041,38 +1055,34 @@ struct RouteArgs {
 };
 
 template <int LG>
-__global__ void __launch_bounds__(256, 4) sparse_route_kernel(const __grid_constant__ RouteArgs ra,
+__global__ void __launch_bounds__(256) sparse_route_kernel(const __grid_constant__ RouteArgs ra,
                                                            const float* __restrict__ grad_rows,
                                                            const int64_t* __restrict__ ids, uint32_t n,
                                                            const __grid_constant__ Geom g) {
-    constexpr int R = 4;
-    const int lane = threadIdx.x % LG;
-    const uint32_t group = (blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = gridDim.x * blockDim.x / LG;
+    __shared__ const float4* s_src[256];
+    __shared__ float4* s_dst[256];
     const int dim4 = g.dim / 4;
-    for (uint32_t k0 = group; k0 < n; k0 += R * ngroups) {
-        float4* wr[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const uint32_t k = k0 + r * ngroups;
-            wr[r] = nullptr;
-            if (k < n) {
-                const int64_t id = ids[k];
-                if (id >= 0 && (uint64_t)id < g.rows) {
-                    uint64_t lrow;
-                    const int o = gpu_of(g, owner_of(g, (uint64_t)id, &lrow));
-                    if (o != g.rank) wr[r] = reinterpret_cast<float4*>(ra.dst[o] + (uint64_t)k * (uint64_t)g.dim);
+    for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
+        const uint32_t k = base + threadIdx.x;
+        const float4* rd = nullptr;
+        float4* wr = nullptr;
+        if (k < n) {
+            const int64_t id = ids[k];
+            if (id >= 0 && (uint64_t)id < g.rows) {
+                uint64_t lrow;
+                const int o = gpu_of(g, owner_of(g, (uint64_t)id, &lrow));
+                if (o != g.rank) {  // owned elsewhere: into that GPU's staging slot for this worker
+                    rd = reinterpret_cast<const float4*>(grad_rows + (uint64_t)k * (uint64_t)g.dim);
+                    wr = reinterpret_cast<float4*>(ra.dst[o] + (uint64_t)k * (uint64_t)g.dim);
                 }
             }
         }
-        for (int c = lane; c < dim4; c += LG) {
-            float4 v[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r)
-                if (wr[r]) v[r] = ldg_row4(grad_rows + (uint64_t)(k0 + r * ngroups) * (uint64_t)g.dim, c);
-#pragma unroll
-            for (int r = 0; r < R; ++r)
-                if (wr[r]) wr[r][c] = v[r];
-        }
+        s_src[threadIdx.x] = rd;
+        s_dst[threadIdx.x] = wr;
+        __syncthreads();
+        const uint32_t left = n - base;
+        copy_tile_rows<LG, 4>(s_src, s_dst, left < 256u ? (int)left : 256, dim4);
+        __syncthreads();
     }
 }
 
@@ -1151,7 +1161,7 @@ extern "C" int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_id
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_ROUTE(LG) \
-    sparse_route_kernel<LG><<<resident_grid(sparse_route_kernel<LG>, 256, want), 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g)
+    sparse_route_kernel<LG><<<resident_grid(sparse_route_kernel<LG>, 256, (n + 255) / 256), 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g)
     switch (lg) {
         case 4: LAUNCH_ROUTE(4); break;
         case 8: LAUNCH_ROUTE(8); break;
