@@ -491,9 +491,13 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
     const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
     const int dim4 = g.dim / 4;
-    for (uint32_t base_u = blockIdx.x * 256u; base_u < n_unique; base_u += gridDim.x * 256u) {
+    // Tile t holds the unique ids t, t + T, t + 2T, ... (T = number of tiles): sorted neighbours --
+    // under Zipf skew the hot ids with their long segments sit together at the front -- are dealt
+    // out over all CTAs instead of landing in one.
+    const uint32_t ntiles = (n_unique + 255u) / 256u;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         {  // phase A
-            const uint32_t u = base_u + threadIdx.x;
+            const uint32_t u = tile + threadIdx.x * ntiles;
             uint32_t s0 = 0, len = 0, cbase = 0;
             float* row = nullptr;
             if (u < n_unique) {
@@ -517,16 +521,15 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
             s_base[threadIdx.x] = cbase;
         }
         __syncthreads();
-        const uint32_t left = n_unique - base_u;
-        const int count = left < 256u ? (int)left : 256;
-        for (int r = grp; r < count; r += GROUPS) {  // phase B
+        for (int r = grp; r < 256; r += GROUPS) {  // phase B
             const uint32_t s0 = s_s0[r], len = s_len[r];
+            float* row = s_row[r];
+            if (row == nullptr) continue;  // past the last unique id
             if (len > SEG_CHUNK) {
                 const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK, cbase = s_base[r];
-                for (uint32_t jj = lane; jj < nchunks; jj += LG) a.chunks[cbase + jj] = make_uint2(base_u + r, jj);
+                for (uint32_t jj = lane; jj < nchunks; jj += LG) a.chunks[cbase + jj] = make_uint2(tile + (uint32_t)r * ntiles, jj);
                 continue;
             }
-            float* row = s_row[r];
             float* arow = ADAGRAD ? s_arow[r] : nullptr;
             for (int c = lane; c < dim4; c += LG) {
                 // the row being updated does not depend on the fold: get it in flight first
