@@ -295,6 +295,19 @@ def sparse_arm(args):
         step()
     sync()
     plan = tab.plan()
+    graph_ms = None
+    if world == 1 and not args.no_graph:  # the same step replayed as one CUDA graph (no per-launch host work)
+        gr = tab.capture_step()
+        for _ in range(3):
+            gr.replay()
+        sync()
+        ga, gb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ga.record()
+        for _ in range(args.steps):
+            gr.replay()
+        gb.record()
+        sync()
+        graph_ms = ga.elapsed_time(gb) / args.steps
     sampler = ClockSampler(local)
     sampler.start()
     l0 = K.launch_count()
@@ -308,6 +321,9 @@ def sparse_arm(args):
     clocks = sampler.finish()
     launches = K.launch_count() - l0
     ms = a.elapsed_time(b) / args.steps
+    launched_ms = ms
+    if graph_ms is not None and graph_ms < ms:
+        ms = graph_ms  # headline = the graph replay; the per-phase breakdown below is from the launched run
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -363,7 +379,8 @@ def sparse_arm(args):
             "metric": "ps_steps_per_sec", "value": round(W * 1e3 / ms, 3), "unit": "worker-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
-            "config": {"workload": label, "n_kept": int(plan["n_kept"]), "n_unique": int(plan["n_unique"]),
+            "config": {"workload": label, "cuda_graph": graph_ms is not None and graph_ms <= launched_ms,
+                       "ms_per_step_launched": round(launched_ms, 4), "n_kept": int(plan["n_kept"]), "n_unique": int(plan["n_unique"]),
                        "longest_segment": int(plan["seg_offset"][1:].astype("int64").__sub__(plan["seg_offset"][:-1]).max()),
                        "l2": "table 2.56 GB and 0.54 GB of gradient rows per step exceed L2; no flush"},
             "ps_steps_per_sec": round(1e3 / ms, 3),

@@ -249,6 +249,22 @@ class EmbeddingTable:
         self.apply()
         self._barrier()  # every shard is updated before anyone pulls again
 
+    def capture_step(self) -> "torch.cuda.CUDAGraph":
+        """pull_step + push_step of one GPU as a CUDA graph: ~25 small launches (radix passes, scans,
+        segments) replayed without per-launch host work.  All counts live on the device and every
+        grid is fixed, so the graph is valid for any ids / gradient rows written into the same
+        buffers.  One GPU only (the cross-rank barriers are not captured)."""
+        if self.world != 1:
+            raise ValueError("capture_step supports one GPU")
+        self.pull_step()
+        self.push_step()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.pull_step()
+            self.push_step()
+        return g
+
     def plan(self) -> dict:
         """The plan of the last sort_segment as NumPy arrays (debug accessor; synchronises)."""
         from .kernels import sparse_plan_read

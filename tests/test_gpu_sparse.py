@@ -219,3 +219,34 @@ def test_embedding_table_host_api(oracle, opt, kind):
     assert np.array_equal(got.view(np.uint32), table.view(np.uint32))
     assert tab.plan()["n_kept"] == W * B
     tab.close()
+
+
+def test_embedding_table_graph_replay_matches(oracle):
+    """One captured pull+push step replayed on new ids / gradient rows gives the oracle's bits."""
+    rows, dim, S, W, B = 20_000, 64, 4, 4, 1024
+    tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd", lr=0.05)
+    tab.init_uniform(1)
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+
+    def load(step):
+        ids = b200ps.synth.make_ids("zipf", rows, W, B, step)
+        grad = oracle.fill_uniform(W * B * dim, 2, step, 0).reshape(W, B, dim)
+        for w in range(W):
+            tab.ids[w].copy_(torch.from_numpy(ids[w]))
+            tab.grad_rows[w].copy_(torch.from_numpy(grad[w]))
+        return ids, grad
+
+    ids, grad = load(1)
+    g = tab.capture_step()  # runs one real step (warm-up), then records one
+    oracle.sparse_apply_sgd(table, 0, grad.reshape(-1, dim), ids.reshape(-1), np.float32(0.25), np.float32(0.05))
+    for step in (2, 3):
+        ids, grad = load(step)
+        torch.cuda.synchronize()
+        g.replay()
+        torch.cuda.synchronize()
+        for w in range(W):
+            assert np.array_equal(tab.pulled[w].cpu().numpy().view(np.uint32), oracle.gather(table, ids[w]).view(np.uint32))
+        oracle.sparse_apply_sgd(table, 0, grad.reshape(-1, dim), ids.reshape(-1), np.float32(0.25), np.float32(0.05))
+    got = np.concatenate([v for _, (_, v) in sorted(tab.dump().items())])
+    assert np.array_equal(got.view(np.uint32), table.view(np.uint32))
+    tab.close()
