@@ -468,6 +468,10 @@ def main():
     sync()
     phases = ps.phase_ms() if ps.profile else None
     ps.profile = False
+    per_rank = None
+    if world > 1 and phases is not None:  # every rank's own kernel times: the step waits for the slowest
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, {k: round(v, 4) for k, v in phases.items()})
     clocks = sampler.finish()
     launches = K.launch_count() - launches0
     ms_total = reduce_max(ev[0].elapsed_time(ev[1]))
@@ -496,7 +500,8 @@ def main():
         roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
                     "traffic": None, "kernel": kname + " (peer loads/stores: NVLink-bound at N>1)", "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
-                    "launches_per_step": n_kernels_step, "phases_ms": {k: round(v, 4) for k, v in phases.items()}}
+                    "launches_per_step": n_kernels_step, "phases_ms": {k: round(v, 4) for k, v in phases.items()},
+                    "phases_ms_per_rank": per_rank}
 
     if roofline is None and world > 1:
         # pipelined multi-GPU step: the exchange is the bound.  Per step a GPU receives the partial
