@@ -48,6 +48,7 @@ def parse():
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-profile", action="store_true", help="N > 1: do not bracket the phases of a step with events")
     ap.add_argument("--no-graph", action="store_true", help="SGD workloads on one GPU: launch every step instead of replaying a CUDA graph")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps, capped at 30")
@@ -455,7 +456,8 @@ def main():
     launches0 = K.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    ps.profile = world > 1 and not ps.overlap
+    ps.profile = world > 1 and not ps.overlap and not args.no_profile
+    host_t0 = time.perf_counter()
     ev[0].record()
     for i in range(args.steps):
         if world == 1:
@@ -465,6 +467,7 @@ def main():
         else:
             do_step()
     ev[1].record()
+    host_ms = 1e3 * (time.perf_counter() - host_t0) / args.steps  # time the host needed to ENQUEUE a step
     sync()
     phases = ps.phase_ms() if ps.profile else None
     ps.profile = False
@@ -573,7 +576,7 @@ def main():
                               ">> 126 MB), no flush needed") if ps.algorithmic_bytes_per_step() > (512 << 20) else
                              (f"working set ({ps.algorithmic_bytes_per_step() / 1e6:.0f} MB per step) fits the 126 MB L2 and is "
                               "NOT flushed between steps: an L2-resident, launch-bound figure, not an HBM one")},
-            "ps_steps_per_sec": round(steps_per_s, 3),
+            "ps_steps_per_sec": round(steps_per_s, 3), "host_enqueue_ms_per_step": round(host_ms, 4),
             "algorithmic_GBps_per_gpu": round(ps.algorithmic_bytes_per_step() / ms_step / 1e6, 1),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
