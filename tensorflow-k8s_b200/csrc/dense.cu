@@ -49,6 +49,7 @@ struct DenseParams {
     float lr;  // SGD: lr.  Adam: lr_t.
     float beta1, beta2, omb1, omb2, eps;
     int load_kind;  // gradient loads: 0 = nc + L1 no-allocate + L2 evict-first, 1 = plain coherent ld.global
+    int end_fence;  // 1: every thread ends with a system-scope fence (drains its peer stores inside the kernel)
 };
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -205,6 +206,7 @@ __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
         }
         for (int k = 0; k < a.n_mirror; ++k) a.mirror[k][j] = p;
     }
+    if (a.end_fence) __threadfence_system();
 }
 
 __device__ __forceinline__ uint64_t hash64(uint64_t key, uint64_t index) {
@@ -298,6 +300,8 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     const Tuning t = g_tuning;
     static const int env_load_kind = getenv("B200PS_DENSE_LOAD") ? atoi(getenv("B200PS_DENSE_LOAD")) : 0;  // experiments
     a.load_kind = env_load_kind;
+    static const int env_end_fence = getenv("B200PS_DENSE_END_FENCE") ? atoi(getenv("B200PS_DENSE_END_FENCE")) : 0;  // experiments
+    a.end_fence = (env_end_fence && a.n_mirror > 0) ? 1 : 0;
     const uint64_t work = a.n4 ? a.n4 : a.n;
     uint64_t want = (work + (uint64_t)t.threads * (uint64_t)t.unroll - 1) / ((uint64_t)t.threads * (uint64_t)t.unroll);
     const uint64_t cap = (uint64_t)sms * (uint64_t)t.ctas_per_sm;

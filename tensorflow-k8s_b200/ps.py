@@ -162,6 +162,9 @@ class ParameterServer:
         self.rank, self.world, self.group, self.transport = rank, world, group, transport
         self.chunk = max(1024, chunk_elems // 1024 * 1024)
         self.t = 0
+        import os as _os
+
+        self._debug_no_mirrors = bool(_os.environ.get("B200PS_DEBUG_NO_MIRRORS"))
         self.trace = None  # a list: the pipelined step appends (label, event) pairs (tools/overlap_timeline.py)
         self.profile = False  # True: step() brackets its phases with CUDA events (see phase_ms)
         self._events: Dict[str, List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = {"fold": [], "apply": []}
@@ -285,16 +288,17 @@ class ParameterServer:
         """One kernel over elements [lo, hi) of slice L (lo/hi in flat-buffer coordinates)."""
         n = hi - lo
         g = _ptrs([self.peer_base[r] + 4 * (off + lo) for r, off in L.grad_src])
-        mir = _ptrs([self.peer_base[r] + 4 * lo for r in L.mirror_ranks])
+        mirror_ranks = [] if self._debug_no_mirrors else L.mirror_ranks  # timing experiments only: results are wrong
+        mir = _ptrs([self.peer_base[r] + 4 * lo for r in mirror_ranks])
         p = C.c_void_p(self.arena.ptr + 4 * lo)
         nbuf = len(L.grad_src)
         if a is None:
-            check(lib.b200ps_dense_apply_sgd(p, g, nbuf, n, self.inv_w, self.lr, mir, len(L.mirror_ranks), self._stream()))
+            check(lib.b200ps_dense_apply_sgd(p, g, nbuf, n, self.inv_w, self.lr, mir, len(mirror_ranks), self._stream()))
         else:
             m, v = self.state[L.shard]
             o = 4 * (lo - L.begin)
             check(lib.b200ps_dense_apply_adam(p, C.c_void_p(m.data_ptr() + o), C.c_void_p(v.data_ptr() + o), g, nbuf, n,
-                                              self.inv_w, C.byref(a), mir, len(L.mirror_ranks), self._stream()))
+                                              self.inv_w, C.byref(a), mir, len(mirror_ranks), self._stream()))
 
     def _step_overlapped(self, a):
         """Two-level aggregation pipelined slice by slice over two streams: the fold stream produces
