@@ -149,6 +149,20 @@ int b200ps_set_dense_tuning(int threads, int ctas_per_sm, int unroll);
 uint64_t b200ps_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
+ * Worker group (SURVEY.md 8(f) rank 1 -- the step on the other side of push / pull).  Reference:
+ * none -- the user's TensorFlow program in the WORKER containers (k8s-operator.md:6, "WORKER
+ * computes").  A real worker for BASELINE configs[0]: the mini-batch gradient of a linear
+ * regression on synthetic data generated in the kernels (x_b[i] = u(seed_x, step, worker*B + b, i),
+ * y_b = x_b . w_true, w_true[i] = u(seed_w, 0, 0, i)); fixed-order double accumulation, one rounding
+ * to float, bit-identical to ps_linreg_grad of the oracle.  d_grad is typically a gradient buffer
+ * of the PS arena (zero-copy push), d_params its replica (zero-copy pull).
+ * ---------------------------------------------------------------------------------------------- */
+size_t b200ps_linreg_scratch_bytes(uint64_t n, int batch);
+int b200ps_linreg_grad(float* d_grad, const float* d_params, uint64_t n, int batch, uint64_t seed_x,
+                       uint64_t seed_w, uint64_t step, uint64_t worker, void* d_scratch, size_t scratch_bytes,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Transport group: buffers other ranks of the box can address.  Reference: none -- TensorFlow's
  * gRPC tensor transport between the PS and WORKER tasks of k8s-operator.md:6.  One process per
  * GPU; each rank exports its gradient / parameter arena, every peer maps it, and the step kernel

@@ -56,6 +56,7 @@ def lib():
         L.ps_sort_segment.argtypes = [vp, u64, vp, vp, vp, vp, vp]
         L.ps_sparse_apply_sgd.argtypes = [vp, i32, C.c_int64, vp, vp, vp, vp, u64, f32, f32]
         L.ps_sparse_apply_adagrad.argtypes = [vp, vp, i32, C.c_int64, vp, vp, vp, vp, u64, f32, f32]
+        L.ps_linreg_grad.argtypes = [vp, vp, u64, i32, u64, u64, u64, u64, i32]
         L.ps_oracle_max_threads.restype = i32
         L.ps_oracle_set_threads.argtypes = [i32]
         _lib = L
@@ -137,6 +138,13 @@ def dense_adam(p, m, v, grads, a: AdamT, threads=1, inv_w=None):
     inv_w = np.float32(1.0) / np.float32(len(grads)) if inv_w is None else np.float32(inv_w)
     lib().ps_dense_adam(_p(p), _p(m), _p(v), C.addressof(gp), len(grads), p.size, inv_w, C.byref(a), threads)
     return p, m, v
+
+
+def linreg_grad(params, batch, seed_x, seed_w, step, worker, threads=1):
+    """Gradient of the mean squared error of one synthetic mini-batch (BASELINE configs[0] worker)."""
+    g = np.empty_like(params)
+    lib().ps_linreg_grad(_p(g), _p(params), params.size, batch, seed_x, seed_w, step, worker, threads)
+    return g
 
 
 def gather(table, ids, row_base=0):

@@ -92,6 +92,29 @@ def dense_adam(p, m, v, grads, a, inv_w=None):
     return p2, m2, v2
 
 
+# ---- 8(f).1: linear-regression worker -----------------------------------------------------------
+
+def linreg_grad(params, batch, seed_x, seed_w, step, worker, block=256):
+    """Same fixed-order double arithmetic as ps_linreg_grad, array-at-a-time."""
+    n = len(params)
+    d = params.astype(np.float64) - uniform(seed_w, 0, 0, 0, n).astype(np.float64)
+    nblk = -(-n // block)
+    X = np.stack([uniform(seed_x, step, worker * batch + b, 0, n) for b in range(batch)]).astype(np.float64)
+    prod = np.zeros((batch, nblk * block))
+    prod[:, :n] = X * d
+    blocks = prod.reshape(batch, nblk, block)
+    acc = np.zeros((batch, nblk))
+    for j in range(block):  # left fold inside each block (padding adds +0.0), then over the blocks
+        acc = acc + blocks[:, :, j]
+    r = np.zeros(batch)
+    for k in range(nblk):
+        r = r + acc[:, k]
+    g = np.zeros(n)
+    for b in range(batch):
+        g = g + X[b] * r[b]
+    return (g * (1.0 / batch)).astype(np.float32)
+
+
 # ---- a10..a12 -----------------------------------------------------------------------------------
 
 def sort_segment(ids):

@@ -172,6 +172,46 @@ void ps_dense_adam(float* p, float* m, float* v, const float* const* grads, int 
     }
 }
 
+/* ---------------------------------------------------------------- 8(f).1: linear-regression worker */
+
+void ps_linreg_grad(float* grad, const float* params, uint64_t n, int batch, uint64_t seed_x, uint64_t seed_w,
+                    uint64_t step, uint64_t worker, int threads) {
+    const uint64_t nblk = (n + PS_LINREG_BLOCK - 1) / PS_LINREG_BLOCK;
+    double* r = (double*)malloc((size_t)batch * sizeof(double));
+    double* part = (double*)malloc((size_t)nblk * sizeof(double));
+    const double inv_b = 1.0 / (double)batch;
+    int b;
+    int64_t i;
+    for (b = 0; b < batch; ++b) {
+        const uint64_t row = worker * (uint64_t)batch + (uint64_t)b;
+        int64_t k;
+        double acc = 0.0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+        for (k = 0; k < (int64_t)nblk; ++k) {
+            uint64_t i0 = (uint64_t)k * PS_LINREG_BLOCK, i1 = i0 + PS_LINREG_BLOCK < n ? i0 + PS_LINREG_BLOCK : n, j;
+            double a = 0.0;
+            for (j = i0; j < i1; ++j) {
+                /* (p - w_true) is formed in double: exact, both are floats */
+                double d = (double)params[j] - (double)ps_uniform(seed_w, 0, 0, j);
+                a = a + (double)ps_uniform(seed_x, step, row, j) * d;
+            }
+            part[k] = a;
+        }
+        for (k = 0; k < (int64_t)nblk; ++k) acc = acc + part[k];
+        r[b] = acc;
+    }
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (i = 0; i < (int64_t)n; ++i) {
+        double acc = 0.0;
+        int bb;
+        for (bb = 0; bb < batch; ++bb)
+            acc = acc + (double)ps_uniform(seed_x, step, worker * (uint64_t)batch + (uint64_t)bb, (uint64_t)i) * r[bb];
+        grad[i] = (float)(inv_b * acc);
+    }
+    free(part);
+    free(r);
+}
+
 /* ---------------------------------------------------------------- a10: gather */
 
 void ps_gather(float* out, const float* table, const int64_t* ids, uint64_t n, int dim,

@@ -86,6 +86,17 @@ void ps_sparse_apply_adagrad(float* table, float* accum, int dim, int64_t row_ba
                              const int64_t* unique_ids, const uint32_t* seg_offset,
                              uint64_t n_unique, float inv_w, float lr);
 
+/* ---- next row 8(f).1: a real worker for BASELINE configs[0] (linear regression) ----
+ * Features x_b[i] = u(seed_x, step, worker*batch + b, i); targets y_b = x_b . w_true with
+ * w_true[i] = u(seed_w, 0, 0, i).  Gradient of (1/2B) sum_b (x_b . p - y_b)^2:
+ *   r_b  = sum_i x_b[i]*(p[i] - w_true[i])       in double, one rounding per multiply and per add:
+ *                                                256-element blocks left to right, then the block sums
+ *                                                left to right
+ *   g[i] = (float)((1/B) * sum_b x_b[i]*r_b)     in double, b = 0..B-1 in order, one rounding to float
+ * The worker is outside the PS path proper (last paragraph); it feeds it real gradients. */
+#define PS_LINREG_BLOCK 256
+void ps_linreg_grad(float* grad, const float* params, uint64_t n, int batch, uint64_t seed_x, uint64_t seed_w,
+                    uint64_t step, uint64_t worker, int threads);
 int ps_oracle_max_threads(void);
 void ps_oracle_set_threads(int n); /* overrides OMP_NUM_THREADS for the calls that follow */
 

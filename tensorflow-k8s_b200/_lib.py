@@ -71,6 +71,8 @@ SIGNATURES = {
     "b200ps_fill_uniform": (_i32, [_vp, _u64, _u64, _u64, _u64, _u64, _vp]),
     "b200ps_set_dense_tuning": (_i32, [_i32, _i32, _i32]),
     "b200ps_launch_count": (_u64, []),
+    "b200ps_linreg_scratch_bytes": (_sz, [_u64, _i32]),
+    "b200ps_linreg_grad": (_i32, [_vp, _vp, _u64, _i32, _u64, _u64, _u64, _u64, _vp, _sz, _vp]),
     "b200ps_dev_alloc": (_i32, [_sz, _pp]),
     "b200ps_dev_free": (_i32, [_vp]),
     "b200ps_ipc_export": (_i32, [_vp, _vp]),

@@ -169,3 +169,16 @@ def sparse_push_sgd_noalloc(shards: Sequence, ids: Sequence, grad_rows: Sequence
     ip = _ptr_array([_ptr_or_int(t, torch.int64, "ids") for t in ids])
     gp = _ptr_array([_ptr_or_int(t, torch.float32, "grad_rows") for t in grad_rows])
     check(lib.b200ps_sparse_push_sgd_noalloc(sb, ip, gp, len(ids), ids_per_worker, C.byref(geom), lr, _stream()))
+
+
+# ---- worker group: a real worker for BASELINE configs[0] ------------------------------------------
+def linreg_grad(grad: torch.Tensor, params: torch.Tensor, batch: int, seed_x: int, seed_w: int, step: int, worker: int,
+                scratch: Optional[torch.Tensor] = None, n: Optional[int] = None) -> torch.Tensor:
+    """grad = d/dp of (1/2B) sum_b (x_b . p - y_b)^2 on the synthetic mini-batch of (step, worker)."""
+    n = params.numel() if n is None else n
+    need = int(lib.b200ps_linreg_scratch_bytes(n, batch))
+    if scratch is None:
+        scratch = torch.empty(need, dtype=torch.uint8, device="cuda")
+    check(lib.b200ps_linreg_grad(_dev_f32(grad, "grad"), _dev_f32(params, "params"), n, batch, seed_x, seed_w, step, worker,
+                                 scratch.data_ptr(), scratch.numel(), _stream()))
+    return grad
