@@ -45,7 +45,7 @@ def test_c0_training_through_the_parameter_server(oracle, nporacle):
     import b200ps
     from b200ps import kernels as K
 
-    n, W, B = 2048, 2, 64
+    n, W, B = 512, 2, 64  # lr = 1 is stable while n / (3 * W * B) < 2
     ps = b200ps.ParameterServer([n], 1, W, optimizer="sgd", lr=1.0)
     ps.init_params(np.zeros(ps.plan.P, np.float32))
     hp = np.zeros(n, np.float32)
