@@ -138,18 +138,21 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs
-def cpu_run(label, sizes, S, W, opt, steps, warmup, seconds=None):
-    """The oracle (oracle/ps_oracle.c, OpenMP, all host threads) on the same workload.
-    Returns (worker_steps_per_s, steps_done, ms_per_step, threads, algorithmic GB/s)."""
+def cpu_run(label, sizes, S, W, opt, steps, warmup, seconds=None, threads=None):
+    """The oracle (oracle/ps_oracle.c, OpenMP, all host threads unless `threads` says otherwise) on
+    the same workload.  Returns (worker_steps_per_s, steps_done, ms_per_step, threads, algorithmic GB/s)."""
     import numpy as np
 
     from oracle import c_oracle as O, np_oracle
 
     nt = O.use_all_cores()
+    fill_threads = nt
+    if threads:
+        nt = threads
     P, _, slices = np_oracle.shard_map(sizes, S, 1024)
-    p = O.fill_uniform(P, 1, 0, 0, threads=nt)
+    p = O.fill_uniform(P, 1, 0, 0, threads=fill_threads)
     m, v = np.zeros(P, np.float32), np.zeros(P, np.float32)
-    g = [O.fill_uniform(P, 2, 1, w, threads=nt) for w in range(W)]
+    g = [O.fill_uniform(P, 2, 1, w, threads=fill_threads) for w in range(W)]
 
     def one(t):
         a = O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t)
@@ -562,6 +565,8 @@ def main():
         cpu = {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
                "sample": f"{done} full steps ({ms:.1f} ms each, {gbs:.0f} GB/s algorithmic) of the same workload within "
                          f"{args.cpu_seconds:.0f} s; substitute CPU reference (oracle/ps_oracle.c, OpenMP)"}
+        v1, d1, ms1, _, g1 = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=args.cpu_seconds / 4, threads=1)
+        cpu["single_thread"] = {"value": round(v1, 3), "ms_per_step": round(ms1, 1), "algorithmic_GBps": round(g1, 1), "steps": d1}
 
     if rank == 0:
         out = {
