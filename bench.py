@@ -390,10 +390,12 @@ def sparse_arm(args):
             "ps_steps_per_sec": round(1e3 / ms, 3),
             "phases_ms": {"serve_pull": round(g_ms, 4), "route+barrier+sort_segment": round(s_ms, 4), "apply": round(p_ms, 4)},
             "roofline": {"bound": "hbm", "achieved": round(gather_bytes / g_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(gather_bytes / g_ms / 1e6 / peak, 4), "traffic": None, "kernel": "sparse_serve_kernel<16>",
+                         "frac": round(gather_bytes / g_ms / 1e6 / peak, 4), "traffic": ncu_traffic("sparse_serve_kernel<16>"),
+                         "kernel": "sparse_serve_kernel<16>",
                          "peak_source": peak_src, "algorithmic_bytes_per_step": gather_bytes},
             "roofline_apply": {"bound": "hbm", "achieved": round(apply_bytes / p_ms / 1e6, 1), "peak": peak, "unit": "GB/s",
-                               "frac": round(apply_bytes / p_ms / 1e6 / peak, 4), "kernel": "sparse_apply_kernel<16,sgd>",
+                               "frac": round(apply_bytes / p_ms / 1e6 / peak, 4), "traffic": ncu_traffic("sparse_apply_kernel<16,sgd>"),
+                               "kernel": "sparse_apply_kernel<16,sgd>",
                                "algorithmic_bytes_per_step": int(apply_bytes)},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}))
     if world > 1:
