@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     constexpr int GROUPS = 256 / LG;
     __shared__ float* s_row[256];
     __shared__ float* s_arow[ADAGRAD ? 256 : 1];
-    __shared__ uint32_t s_s0[256], s_len[256], s_base[256];
+    __shared__ uint32_t s_s0[256], s_len[256], s_base[256], s_first[256];
     const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
     const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
     const int dim4 = g.dim / 4;
@@ -498,11 +498,12 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         {  // phase A
             const uint32_t u = tile + threadIdx.x * ntiles;
-            uint32_t s0 = 0, len = 0, cbase = 0;
+            uint32_t s0 = 0, len = 0, cbase = 0, first = 0;
             float* row = nullptr;
             if (u < n_unique) {
                 s0 = a.seg_off[u];
                 len = a.seg_off[u + 1] - s0;
+                first = a.perm[s0];  // source entry of the segment's first row: one dependent load less in phase B
                 uint64_t lrow;
                 const int s = owner_of(g, a.unique[u], &lrow);
                 row = tb.base[s] + lrow * (uint64_t)g.dim;
@@ -519,6 +520,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
             s_s0[threadIdx.x] = s0;
             s_len[threadIdx.x] = len;
             s_base[threadIdx.x] = cbase;
+            s_first[threadIdx.x] = first;
         }
         __syncthreads();
         for (int r = grp; r < 256; r += GROUPS) {  // phase B
@@ -536,7 +538,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
                 float4 rv = reinterpret_cast<const float4*>(row)[c];
                 float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (ADAGRAD) ac = reinterpret_cast<const float4*>(arow)[c];
-                float4 acc = ldg_row4(grad_row(gs, a.perm[s0], g.dim), c);
+                float4 acc = ldg_row4(grad_row(gs, s_first[r], g.dim), c);
                 acc = fold_rows(acc, gs, a.perm, s0 + 1, s0 + len, g.dim, c);
                 rv.x = upd1<ADAGRAD>(acc.x, rv.x, ac.x, a.inv_w, a.lr);
                 rv.y = upd1<ADAGRAD>(acc.y, rv.y, ac.y, a.inv_w, a.lr);
