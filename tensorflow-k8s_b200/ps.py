@@ -160,6 +160,9 @@ class ParameterServer:
         self.plan = build_plan(self.map, num_workers, rank, world, aggregate)
         self.optimizer, self.lr, self.betas, self.eps = optimizer, lr, (beta1, beta2), eps
         self.rank, self.world, self.group, self.transport = rank, world, group, transport
+        import os as _os0
+
+        chunk_elems = int(_os0.environ.get("B200PS_HOST_CHUNK_ELEMS", chunk_elems))  # pipeline granularity (experiments)
         self.chunk = max(1024, chunk_elems // 1024 * 1024)
         self.t = 0
         import os as _os
@@ -192,6 +195,7 @@ class ParameterServer:
         self.peer_base: Dict[int, int] = {rank: self.arena.ptr}
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._s_in, self._s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        self._d2h_done: Dict[int, torch.cuda.Event] = {}  # per chunk: the last step_host's copy-out
         if world > 1:
             self._exchange_handles()
             self._flag_ptrs = _ptrs([self.peer_base[r] + 4 * self.plan.arena_elems_of(r) for r in range(world)])
@@ -445,7 +449,9 @@ class ParameterServer:
     def step_host(self, host_grads: Dict[int, torch.Tensor], host_out: Dict[int, torch.Tensor]):
         """A whole step with HOST buffers: every local worker's gradient goes host -> device, the
         step runs, and the updated parameters go device -> host into every local worker's buffer.
-        With one GPU the three phases are pipelined chunk by chunk over three streams."""
+        With one GPU the three phases are pipelined chunk by chunk over three streams, and the
+        copy-out of one step overlaps the copy-in of the next; call host_sync() (or synchronise the
+        device) before reading the host buffers."""
         if self.world > 1:
             for w, h in host_grads.items():
                 self.push(w, h)
@@ -456,7 +462,10 @@ class ParameterServer:
         self.t += 1
         a = self._opt_scalars()
         cur = torch.cuda.current_stream()
+        # this step's H2D may start once the previous step's kernels are done with the gradient
+        # buffers; it does NOT wait for the previous step's D2H (other PCIe direction)
         self._s_in.wait_stream(cur)
+        ci = 0
         for L in self.plan.launches:
             for lo in range(L.begin, L.end, self.chunk):
                 hi = min(lo + self.chunk, L.end)
@@ -466,6 +475,9 @@ class ParameterServer:
                     ev = torch.cuda.Event()
                     ev.record(self._s_in)
                 cur.wait_event(ev)
+                prev = self._d2h_done.get(ci)
+                if prev is not None:
+                    cur.wait_event(prev)  # the previous step's copy-out of this chunk has left the replica
                 self._launch(L, lo, hi, a)
                 ev2 = torch.cuda.Event()
                 ev2.record(cur)
@@ -473,7 +485,14 @@ class ParameterServer:
                 with torch.cuda.stream(self._s_out):
                     for w, h in host_out.items():
                         h[lo:hi].copy_(self.replica[lo:hi], non_blocking=True)
-        cur.wait_stream(self._s_out)
+                    ev3 = torch.cuda.Event()
+                    ev3.record(self._s_out)
+                self._d2h_done[ci] = ev3
+                ci += 1
+
+    def host_sync(self):
+        """Blocks until the host buffers of the last step_host() hold the pulled parameters."""
+        self._s_out.synchronize()
 
     # ---- inspection ---------------------------------------------------------------------------
     def dump(self) -> Dict[int, Dict[str, np.ndarray]]:
