@@ -340,18 +340,20 @@ class ParameterServer:
         with torch.cuda.stream(self._s_out):
             # few CTAs: the apply is NVLink-latency-bound and must leave SM slots to the folds
             check(lib.b200ps_set_dense_tuning(*self.overlap_apply_geometry))
-            err = C.c_void_p(self.arena.ptr + 4 * (self.plan.arena_elems + 9))
-            for L in self.plan.launches:
-                mask = 0
-                for r, _ in L.grad_src:
-                    mask |= 1 << r
-                check(lib.b200ps_peer_wait(C.c_void_p(flag_base(self.rank) + 4 * L.shard * SLICE_FLAG_STRIDE), mask, e, err,
-                                           self._stream()))
-                tick(f"wait {L.shard}")
-                if L.end > L.begin:
-                    self._launch(L, L.begin, L.end, a)
-                tick(f"apply {L.shard}")
-            check(lib.b200ps_set_dense_tuning(256, 8, 2))
+            try:
+                err = C.c_void_p(self.arena.ptr + 4 * (self.plan.arena_elems + 9))
+                for L in self.plan.launches:
+                    mask = 0
+                    for r, _ in L.grad_src:
+                        mask |= 1 << r
+                    check(lib.b200ps_peer_wait(C.c_void_p(flag_base(self.rank) + 4 * L.shard * SLICE_FLAG_STRIDE), mask, e, err,
+                                               self._stream()))
+                    tick(f"wait {L.shard}")
+                    if L.end > L.begin:
+                        self._launch(L, L.begin, L.end, a)
+                    tick(f"apply {L.shard}")
+            finally:
+                check(lib.b200ps_set_dense_tuning(256, 8, 2))  # the process-wide default geometry
         cur.wait_stream(self._s_in)
         cur.wait_stream(self._s_out)
         tick("joined")
