@@ -182,3 +182,18 @@ def linreg_grad(grad: torch.Tensor, params: torch.Tensor, batch: int, seed_x: in
     check(lib.b200ps_linreg_grad(_dev_f32(grad, "grad"), _dev_f32(params, "params"), n, batch, seed_x, seed_w, step, worker,
                                  scratch.data_ptr(), scratch.numel(), _stream()))
     return grad
+
+
+def sparse_serve(outs: Sequence, shards: Sequence, ids: Sequence, ids_per_worker: int, geom: TableGeom) -> None:
+    """Owner side of pull for all workers: rows of this GPU's shards -> outs[w] (tensor or raw peer pointer)."""
+    op = _ptr_array([_ptr_or_int(t, torch.float32, "out") for t in outs])
+    sb = _ptr_array([_ptr_or_int(t, torch.float32, "shard") if t is not None else 0 for t in shards])
+    ip = _ptr_array([_ptr_or_int(t, torch.int64, "ids") for t in ids])
+    check(lib.b200ps_sparse_serve(op, sb, ip, len(ids), ids_per_worker, C.byref(geom), _stream()))
+
+
+def sparse_route(grad_rows: torch.Tensor, ids: torch.Tensor, geom: TableGeom, dst_by_gpu: Sequence) -> None:
+    """Worker side of push: rows owned by GPU o go to dst_by_gpu[o] (None for this GPU)."""
+    dp = _ptr_array([_ptr_or_int(t, torch.float32, "staging") if t is not None else 0 for t in dst_by_gpu])
+    check(lib.b200ps_sparse_route(_dev(grad_rows, torch.float32, "grad_rows"), _dev(ids, torch.int64, "ids"), ids.numel(),
+                                  C.byref(geom), dp, _stream()))

@@ -250,3 +250,43 @@ def test_embedding_table_graph_replay_matches(oracle):
     got = np.concatenate([v for _, (_, v) in sorted(tab.dump().items())])
     assert np.array_equal(got.view(np.uint32), table.view(np.uint32))
     tab.close()
+
+
+@pytest.mark.parametrize("dim,world", [(4, 2), (8, 3), (32, 2), (128, 3), (256, 4)])
+def test_serve_and_route_with_emulated_ranks(oracle, dim, world):
+    """The multi-GPU routing on ONE device: every 'rank' runs serve over all workers' ids and the
+    union fills every worker's rows; every worker's 'GPU' routes the rows other ranks own into their
+    staging buffers and each rank's sort + apply reads local-or-staged rows only.  All lane-group
+    widths (dim 4 .. 256) and an out-of-range id are exercised; result = the oracle's full update."""
+    rows, S, W, B = 5000, 6, 4, 700
+    rng = np.random.default_rng(dim * 10 + world)
+    ids = rng.integers(0, rows, (W, B)).astype(np.int64)
+    ids[1, 5] = -3  # out of range: pulled as zeros, dropped by the push
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0).reshape(rows, dim)
+    grad = oracle.fill_uniform(W * B * dim, 2, 1, 0).reshape(W, B, dim)
+    dt = dev(table)
+    dids, dgr = [dev(ids[w]) for w in range(W)], [dev(grad[w]) for w in range(W)]
+    my_shards = lambda r: [t if s % world == r else None for s, t in enumerate(shard_views(dt, rows, S))]
+    # pull
+    outs = [torch.full((B, dim), float("nan"), device="cuda") for _ in range(W)]
+    for r in range(world):
+        K.sparse_serve(outs, my_shards(r), dids, B, K.table_geom(rows, dim, S, r, world))
+    for w in range(W):
+        want = oracle.gather(table, np.where(ids[w] < 0, 0, ids[w]))
+        want[ids[w] < 0] = 0.0
+        assert np.array_equal(outs[w].cpu().numpy().view(np.uint32), want.view(np.uint32))
+    # push
+    staging = {(o, w): torch.full((B, dim), float("nan"), device="cuda") for o in range(world) for w in range(W) if w % world != o}
+    for w in range(W):
+        rw = w % world
+        K.sparse_route(dgr[w], dids[w], K.table_geom(rows, dim, S, rw, world), [None if o == rw else staging[(o, w)] for o in range(world)])
+    ws = K.sparse_workspace(W * B, dim)
+    for r in range(world):
+        geom = K.table_geom(rows, dim, S, r, world)
+        rows_for = [dgr[w] if w % world == r else staging[(r, w)] for w in range(W)]
+        K.sparse_sort_segment(dids, B, geom, ws)
+        K.sparse_apply_sgd(my_shards(r), rows_for, B, geom, 0.05, ws)
+    keep = ids.reshape(-1) >= 0
+    oracle.sparse_apply_sgd(table, 0, np.ascontiguousarray(grad.reshape(-1, dim)[keep]), ids.reshape(-1)[keep],
+                            np.float32(1.0) / np.float32(W), np.float32(0.05))
+    assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
