@@ -601,41 +601,63 @@ __global__ void __launch_bounds__(256) long_final_kernel(const __grid_constant__
 }
 
 // ------------------------------------------------------------------------------------------------
-// a10: gather
+// a10: gather (single-worker pull; the all-worker owner-side form is sparse_serve_kernel below)
 // ------------------------------------------------------------------------------------------------
-template <int LG>
-__global__ void __launch_bounds__(256) sparse_gather_kernel(float* __restrict__ out, const __grid_constant__ ShardBases tb,
-                                                            const __grid_constant__ Geom g, const int64_t* __restrict__ ids,
-                                                            uint64_t n) {
-    constexpr int R = 4;  // rows in flight per lane group
-    const int lane = threadIdx.x % LG;
-    const uint64_t group = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LG, ngroups = (uint64_t)gridDim.x * blockDim.x / LG;
-    const int dim4 = g.dim / 4;
-    for (uint64_t k0 = group; k0 < n; k0 += R * ngroups) {
-        const float4* src[R];
+// Copies the rows described in shared memory: entry k of the tile goes from s_src[k] to s_dst[k]
+// (null dst: not this GPU's business; null src with a dst: an out-of-range id, answered with zeros).
+// One lane group per row, R rows in flight per group.
+template <int LG, int R>
+__device__ __forceinline__ void copy_tile_rows(const float4* const* s_src, float4* const* s_dst, int count, int dim4) {
+    constexpr int GROUPS = 256 / LG;
+    const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
+    for (int r0 = grp; r0 < count; r0 += GROUPS * R) {
+        const float4* rd[R];
+        float4* wr[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const uint64_t k = k0 + (uint64_t)r * ngroups;
-            src[r] = nullptr;
-            if (k < n) {
-                const int64_t id = ids[k];
-                if (id >= 0 && (uint64_t)id < g.rows) {
-                    uint64_t lrow;
-                    const int s = owner_of(g, (uint64_t)id, &lrow);
-                    src[r] = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
-                }
-            }
+        for (int k = 0; k < R; ++k) {
+            const int r = r0 + k * GROUPS;
+            rd[k] = r < count ? s_src[r] : nullptr;
+            wr[k] = r < count ? s_dst[r] : nullptr;
         }
         for (int c = lane; c < dim4; c += LG) {
             float4 v[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) v[r] = src[r] ? src[r][c] : make_float4(0.f, 0.f, 0.f, 0.f);  // bad id: zero row
+            for (int k = 0; k < R; ++k) v[k] = rd[k] ? rd[k][c] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const uint64_t k = k0 + (uint64_t)r * ngroups;
-                if (k < n) reinterpret_cast<float4*>(out + k * (uint64_t)g.dim)[c] = v[r];
+            for (int k = 0; k < R; ++k)
+                if (wr[k]) wr[k][c] = v[k];
+        }
+    }
+}
+
+// Tiles of 256 ids, two phases (as in sparse_serve_kernel): one thread per id resolves the source
+// row once into shared memory, then one lane group per row copies it.
+template <int LG>
+__global__ void __launch_bounds__(256) sparse_gather_kernel(float* __restrict__ out, const __grid_constant__ ShardBases tb,
+                                                            const __grid_constant__ Geom g, const int64_t* __restrict__ ids,
+                                                            uint64_t n) {
+    __shared__ const float4* s_src[256];
+    __shared__ float4* s_dst[256];
+    const int dim4 = g.dim / 4;
+    for (uint64_t base = (uint64_t)blockIdx.x * 256u; base < n; base += (uint64_t)gridDim.x * 256u) {
+        const uint64_t k = base + threadIdx.x;
+        const float4* rd = nullptr;
+        float4* wr = nullptr;
+        if (k < n) {
+            const int64_t id = ids[k];
+            wr = reinterpret_cast<float4*>(out + k * (uint64_t)g.dim);
+            if (id >= 0 && (uint64_t)id < g.rows) {  // an out-of-range id keeps rd null: a row of zeros
+                uint64_t lrow;
+                const int s = owner_of(g, (uint64_t)id, &lrow);
+                rd = reinterpret_cast<const float4*>(tb.base[s] + lrow * (uint64_t)g.dim);
             }
         }
+        s_src[threadIdx.x] = rd;
+        s_dst[threadIdx.x] = wr;
+        __syncthreads();
+        const uint64_t left = n - base;
+        copy_tile_rows<LG, 4>(s_src, s_dst, left < 256u ? (int)left : 256, dim4);
+        __syncthreads();
     }
 }
 
@@ -789,7 +811,7 @@ extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_ba
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_GATHER(LG) \
-    sparse_gather_kernel<LG><<<resident_grid(sparse_gather_kernel<LG>, 256, want), 256, 0, st>>>(d_out, tb, g, d_ids, n)
+    sparse_gather_kernel<LG><<<resident_grid(sparse_gather_kernel<LG>, 256, (n + 255) / 256), 256, 0, st>>>(d_out, tb, g, d_ids, n)
     switch (lg) {
         case 4: LAUNCH_GATHER(4); break;
         case 8: LAUNCH_GATHER(8); break;
@@ -990,33 +1012,6 @@ namespace {
 struct ServeArgs {
     float* out[B200PS_MAX_WORKERS];  // worker w's pulled rows [B, dim]
 };
-
-// Copies the rows described in shared memory: entry k of the tile goes from s_src[k] to s_dst[k]
-// (null dst: not this GPU's business; null src with a dst: an out-of-range id, answered with zeros).
-// One lane group per row, R rows in flight per group.
-template <int LG, int R>
-__device__ __forceinline__ void copy_tile_rows(const float4* const* s_src, float4* const* s_dst, int count, int dim4) {
-    constexpr int GROUPS = 256 / LG;
-    const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
-    for (int r0 = grp; r0 < count; r0 += GROUPS * R) {
-        const float4* rd[R];
-        float4* wr[R];
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-            const int r = r0 + k * GROUPS;
-            rd[k] = r < count ? s_src[r] : nullptr;
-            wr[k] = r < count ? s_dst[r] : nullptr;
-        }
-        for (int c = lane; c < dim4; c += LG) {
-            float4 v[R];
-#pragma unroll
-            for (int k = 0; k < R; ++k) v[k] = rd[k] ? rd[k][c] : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int k = 0; k < R; ++k)
-                if (wr[k]) wr[k][c] = v[k];
-        }
-    }
-}
 
 // Two phases per tile of 256 entries.  A: one THREAD per entry reads its id (coalesced), does the
 // owner / worker arithmetic once and leaves a (source row, destination row) pair in shared memory.
