@@ -134,6 +134,11 @@ int b200ps_dense_apply_sgd(float* d_params, const float* const* d_grads, int W, 
 int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float* const* d_grads,
                             int W, uint64_t n, float inv_w, const b200ps_adam_t* opt,
                             float* const* d_mirrors, int n_mirrors, void* stream);
+/* TensorFlow's ApplyMomentum (no Nesterov): accum = momentum*accum + g; p -= lr*accum.
+ * (more optimizers.) */
+int b200ps_dense_apply_momentum(float* d_params, float* d_accum, const float* const* d_grads, int W,
+                                uint64_t n, float inv_w, float lr, float momentum,
+                                float* const* d_mirrors, int n_mirrors, void* stream);
 /* d_out[i] = ((b_0[i] + b_1[i]) + b_2[i]) + ...  -- the local half of the two-level aggregation:
  * a GPU that hosts several workers folds their gradients once (in worker order), and only that
  * partial sum crosses NVLink; the owning shard then folds the G partials in GPU order. */

@@ -78,6 +78,12 @@ def dense_sgd(p, grads, lr, inv_w=None):
     return p - np.float32(lr) * g
 
 
+def dense_momentum(p, accum, grads, lr, momentum, inv_w=None):
+    g = aggregate(grads, np.float32(1.0) / np.float32(len(grads)) if inv_w is None else inv_w)
+    a2 = np.float32(momentum) * accum + g
+    return p - np.float32(lr) * a2, a2
+
+
 def adam_scalars(lr: float, beta1: float, beta2: float, eps: float, t: int):
     lr_t = np.float32(lr * np.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t))
     return dict(lr_t=lr_t, beta1=np.float32(beta1), beta2=np.float32(beta2),

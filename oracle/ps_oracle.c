@@ -117,6 +117,28 @@ void ps_dense_sgd(float* p, const float* const* grads, int W, uint64_t n, float 
     }
 }
 
+void ps_dense_momentum(float* p, float* accum, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
+                       float momentum, int threads) {
+    int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (b = 0; b < nb; ++b) {
+        float acc[BLK];
+        uint64_t i0 = (uint64_t)b * BLK, len = n - i0 < BLK ? n - i0 : BLK, i;
+        int w;
+        for (i = 0; i < len; ++i) acc[i] = grads[0][i0 + i];
+        for (w = 1; w < W; ++w) {
+            const float* g = grads[w] + i0;
+            for (i = 0; i < len; ++i) acc[i] = acc[i] + g[i];
+        }
+        for (i = 0; i < len; ++i) {
+            float g = acc[i] * inv_w;
+            float an = momentum * accum[i0 + i] + g;
+            accum[i0 + i] = an;
+            p[i0 + i] = p[i0 + i] - lr * an;
+        }
+    }
+}
+
 void ps_dense_fold(float* dst, const float* const* bufs, int W, uint64_t n, int threads) {
     /* the local half of the two-level aggregation: dst = ((b0 + b1) + b2) + ..., no scaling */
     int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;

@@ -45,6 +45,9 @@ int     ps_row_owner(uint64_t rows, int nshards, uint64_t id);
 /* g = inv_w * (((g0 + g1) + g2) + ...);  p -= lr * g */
 void ps_dense_sgd(float* p, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
                   int threads);
+/* TF ApplyMomentum (no Nesterov): accum = momentum*accum + g;  p -= lr*accum */
+void ps_dense_momentum(float* p, float* accum, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
+                       float momentum, int threads);
 /* dst = ((b0 + b1) + b2) + ... (two-level aggregation: the per-GPU partial sum; the partials are
  * then folded in GPU order by ps_dense_* with inv_w = 1 / total workers) */
 void ps_dense_fold(float* dst, const float* const* bufs, int W, uint64_t n, int threads);

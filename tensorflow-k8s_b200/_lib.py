@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200ps_dense_apply_sgd": (_i32, [_vp, _vp, _i32, _u64, _f32, _f32, _vp, _i32, _vp]),
     "b200ps_dense_apply_adam": (_i32, [_vp, _vp, _vp, _vp, _i32, _u64, _f32, C.POINTER(AdamScalars), _vp, _i32, _vp]),
     "b200ps_dense_fold": (_i32, [_vp, _vp, _i32, _u64, _vp]),
+    "b200ps_dense_apply_momentum": (_i32, [_vp, _vp, _vp, _i32, _u64, _f32, _f32, _f32, _vp, _i32, _vp]),
     "b200ps_fill_uniform": (_i32, [_vp, _u64, _u64, _u64, _u64, _u64, _vp]),
     "b200ps_set_dense_tuning": (_i32, [_i32, _i32, _i32]),
     "b200ps_launch_count": (_u64, []),

@@ -33,7 +33,9 @@ std::atomic<uint64_t> g_launches{0};
 
 namespace {
 
-enum { OPT_SGD = 0, OPT_ADAM = 1, OPT_FOLD = 2 };  // FOLD: p[i] = left fold of the buffers, nothing else
+enum { OPT_SGD = 0, OPT_ADAM = 1, OPT_FOLD = 2, OPT_MOMENTUM = 3 };  // FOLD: p[i] = left fold of the buffers, nothing else
+#define HAS_M(OPT) ((OPT) == OPT_ADAM || (OPT) == OPT_MOMENTUM)  /* first state buffer: Adam's m / the momentum accumulator */
+#define HAS_V(OPT) ((OPT) == OPT_ADAM)
 
 struct DenseParams {
     const float* g[B200PS_MAX_WORKERS];
@@ -99,6 +101,9 @@ __device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, 
     const float g = __fmul_rn(sum, a.inv_w);
     if (OPT == OPT_SGD) {
         p = __fsub_rn(p, __fmul_rn(a.lr, g));
+    } else if (OPT == OPT_MOMENTUM) {  // TF ApplyMomentum: accum = momentum*accum + g; p -= lr*accum
+        m = __fadd_rn(__fmul_rn(a.beta1, m), g);
+        p = __fsub_rn(p, __fmul_rn(a.lr, m));
     } else {
         m = __fadd_rn(__fmul_rn(a.beta1, m), __fmul_rn(a.omb1, g));
         v = __fadd_rn(__fmul_rn(a.beta2, v), __fmul_rn(a.omb2, __fmul_rn(g, g)));
@@ -129,10 +134,8 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (OPT != OPT_FOLD) P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
-            if (OPT == OPT_ADAM) {
-                M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
-                V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
-            }
+            if (HAS_M(OPT)) M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
+            if (HAS_V(OPT)) V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -144,10 +147,8 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (OPT != OPT_FOLD) P[u] = ld_state(reinterpret_cast<const float4*>(a.p) + i + u * stride);
-            if (OPT == OPT_ADAM) {
-                M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
-                V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
-            }
+            if (HAS_M(OPT)) M[u] = ld_state(reinterpret_cast<const float4*>(a.m) + i + u * stride);
+            if (HAS_V(OPT)) V[u] = ld_state(reinterpret_cast<const float4*>(a.v) + i + u * stride);
             acc[u] = ld_once(reinterpret_cast<const float4*>(a.g[0]) + i + u * stride, pol, a.load_kind);
         }
         for (int w0 = 1; w0 < a.W; w0 += 4) {
@@ -172,10 +173,8 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
         apply4<OPT>(acc[u], P[u], M[u], V[u], a);
         const uint64_t j = i + u * stride;
         st_f4(reinterpret_cast<float4*>(a.p) + j, P[u]);
-        if (OPT == OPT_ADAM) {
-            st_f4(reinterpret_cast<float4*>(a.m) + j, M[u]);
-            st_f4(reinterpret_cast<float4*>(a.v) + j, V[u]);
-        }
+        if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + j, M[u]);
+        if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + j, V[u]);
         for (int k = 0; k < a.n_mirror; ++k) st_f4(reinterpret_cast<float4*>(a.mirror[k]) + j, P[u]);
     }
 }
@@ -194,16 +193,12 @@ __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
         float s = a.g[0][j];
         for (int w = 1; w < a.W; ++w) s = __fadd_rn(s, a.g[w][j]);
         float p = OPT == OPT_FOLD ? 0.f : a.p[j], m = 0.f, v = 0.f;
-        if (OPT == OPT_ADAM) {
-            m = a.m[j];
-            v = a.v[j];
-        }
+        if (HAS_M(OPT)) m = a.m[j];
+        if (HAS_V(OPT)) v = a.v[j];
         apply1<OPT>(s, p, m, v, a);
         a.p[j] = p;
-        if (OPT == OPT_ADAM) {
-            a.m[j] = m;
-            a.v[j] = v;
-        }
+        if (HAS_M(OPT)) a.m[j] = m;
+        if (HAS_V(OPT)) a.v[j] = v;
         for (int k = 0; k < a.n_mirror; ++k) a.mirror[k][j] = p;
     }
     if (a.end_fence) __threadfence_system();
@@ -280,6 +275,7 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
                    "n_mirrors = %d is outside 0..%d", a.n_mirror, B200PS_MAX_MIRRORS);
     B200PS_REQUIRE(a.n_mirror == 0 || d_mirrors, B200PS_ERR_INVALID, "null mirror list");
     if (opt == OPT_ADAM) B200PS_REQUIRE(a.m && a.v, B200PS_ERR_INVALID, "Adam needs m and v");
+    if (opt == OPT_MOMENTUM) B200PS_REQUIRE(a.m, B200PS_ERR_INVALID, "momentum needs the accumulator");
     if (a.n == 0) return B200PS_OK;
 
     uintptr_t bits = (uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v;
@@ -309,6 +305,7 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t e = opt == OPT_SGD    ? launch_w<OPT_SGD>(a, grid, t.threads, t.unroll, st)
                     : opt == OPT_ADAM ? launch_w<OPT_ADAM>(a, grid, t.threads, t.unroll, st)
+                    : opt == OPT_MOMENTUM ? launch_w<OPT_MOMENTUM>(a, grid, t.threads, t.unroll, st)
                                       : launch_w<OPT_FOLD>(a, grid, t.threads, t.unroll, st);
     B200PS_CUDA(e);
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -372,6 +369,21 @@ extern "C" int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, 
     a.omb2 = opt->omb2;
     a.eps = opt->eps;
     return dense_apply(OPT_ADAM, a, d_grads, d_mirrors, stream);
+}
+
+extern "C" int b200ps_dense_apply_momentum(float* d_params, float* d_accum, const float* const* d_grads, int W, uint64_t n,
+                                           float inv_w, float lr, float momentum, float* const* d_mirrors, int n_mirrors,
+                                           void* stream) {
+    DenseParams a{};
+    a.p = d_params;
+    a.m = d_accum;
+    a.n = n;
+    a.W = W;
+    a.inv_w = inv_w;
+    a.n_mirror = n_mirrors;
+    a.lr = lr;
+    a.beta1 = momentum;
+    return dense_apply(OPT_MOMENTUM, a, d_grads, d_mirrors, stream);
 }
 
 extern "C" int b200ps_fill_uniform(float* d_dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,

@@ -61,6 +61,17 @@ def dense_apply_adam(params: torch.Tensor, m: torch.Tensor, v: torch.Tensor, gra
                                       inv_w, C.byref(opt), mi, len(mirrors), _stream()))
 
 
+def dense_apply_momentum(params: torch.Tensor, accum: torch.Tensor, grads: Sequence[torch.Tensor], lr: float, momentum: float,
+                         mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None, inv_w: Optional[float] = None) -> None:
+    """accum = momentum*accum + g; params -= lr*accum (TensorFlow's ApplyMomentum, no Nesterov)."""
+    n = params.numel() if n is None else n
+    inv_w = inv_w_f32(max(len(grads), 1)) if inv_w is None else inv_w
+    g = _ptr_array([_dev_f32(t, "grad") for t in grads])
+    mi = _ptr_array([_dev_f32(t, "mirror") for t in mirrors])
+    check(lib.b200ps_dense_apply_momentum(_dev_f32(params, "params"), _dev_f32(accum, "accum"), g, len(grads), n, inv_w, lr,
+                                          momentum, mi, len(mirrors), _stream()))
+
+
 def dense_fold(out: torch.Tensor, bufs: Sequence[torch.Tensor], n: Optional[int] = None) -> torch.Tensor:
     """out = ((b0 + b1) + b2) + ... : the per-GPU partial sum of the two-level aggregation."""
     n = out.numel() if n is None else n

@@ -147,11 +147,13 @@ class ParameterServer:
     def __init__(self, var_numel: Sequence[int], num_shards: int, num_workers: int, optimizer: str = "adam",
                  lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, rank: int = 0,
                  world: int = 1, group=None, transport: str = "peer", chunk_elems: int = 4 << 20,
-                 aggregate: str = "flat", barrier: str = "nccl", overlap: bool = False):
+                 aggregate: str = "flat", barrier: str = "nccl", overlap: bool = False, momentum: float = 0.9):
         if barrier not in ("peer", "nccl"):
             raise ValueError("barrier must be 'peer' (flags in peer memory) or 'nccl' (a 4-byte all-reduce)")
-        if optimizer not in ("sgd", "adam"):
-            raise ValueError("optimizer must be 'sgd' or 'adam'")
+        if optimizer not in ("sgd", "adam", "momentum"):
+            raise ValueError("optimizer must be 'sgd', 'momentum' or 'adam'")
+        if optimizer == "momentum" and transport == "nccl":
+            raise ValueError("transport='nccl' supports 'sgd' and 'adam'")
         if transport not in ("peer", "nccl"):
             raise ValueError("transport must be 'peer' or 'nccl'")
         if not torch.cuda.is_available():
@@ -187,11 +189,12 @@ class ParameterServer:
                                                for i, w in enumerate(self.plan.local_workers)}
         self.inv_w = float(np.float32(1.0) / np.float32(num_workers))
         self.state: Dict[int, Tuple[torch.Tensor, torch.Tensor]] = {}
-        if optimizer == "adam":
+        self.momentum = momentum
+        if optimizer in ("adam", "momentum"):  # Adam: (m, v); momentum: (accumulator, nothing)
             for L in self.plan.launches:
                 n = L.end - L.begin
                 self.state[L.shard] = (torch.zeros(n, dtype=torch.float32, device="cuda"),
-                                       torch.zeros(n, dtype=torch.float32, device="cuda"))
+                                       torch.zeros(n if optimizer == "adam" else 0, dtype=torch.float32, device="cuda"))
         self.peer_base: Dict[int, int] = {rank: self.arena.ptr}
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._s_in, self._s_out = torch.cuda.Stream(), torch.cuda.Stream()
@@ -296,7 +299,11 @@ class ParameterServer:
         mir = _ptrs([self.peer_base[r] + 4 * lo for r in mirror_ranks])
         p = C.c_void_p(self.arena.ptr + 4 * lo)
         nbuf = len(L.grad_src)
-        if a is None:
+        if self.optimizer == "momentum":
+            acc, _ = self.state[L.shard]
+            check(lib.b200ps_dense_apply_momentum(p, C.c_void_p(acc.data_ptr() + 4 * (lo - L.begin)), g, nbuf, n, self.inv_w,
+                                                  self.lr, self.momentum, mir, len(mirror_ranks), self._stream()))
+        elif a is None:
             check(lib.b200ps_dense_apply_sgd(p, g, nbuf, n, self.inv_w, self.lr, mir, len(mirror_ranks), self._stream()))
         else:
             m, v = self.state[L.shard]
@@ -390,8 +397,8 @@ class ParameterServer:
         1 M-parameter step is ~3 us of kernel time behind ~25 us of host-side launch work.  SGD on
         one GPU only: Adam's bias-corrected step size is a launch parameter that changes every
         step, and the cross-rank barriers are not captured."""
-        if self.optimizer != "sgd" or self.world != 1:
-            raise ValueError("capture_step supports SGD on one GPU")
+        if self.optimizer not in ("sgd", "momentum") or self.world != 1:
+            raise ValueError("capture_step supports SGD / momentum on one GPU")
         self.step()  # warm up outside the capture
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
@@ -505,7 +512,10 @@ class ParameterServer:
         for L in self.plan.launches:
             d = {"range": (L.begin, L.end), "p": self.replica[L.begin:L.end].cpu().numpy()}
             if L.shard in self.state:
-                d["m"], d["v"] = (x.cpu().numpy() for x in self.state[L.shard])
+                m, v = self.state[L.shard]
+                d["m"] = m.cpu().numpy()  # Adam's m, or the momentum accumulator
+                if v.numel():
+                    d["v"] = v.cpu().numpy()
             out[L.shard] = d
         return out
 
@@ -544,7 +554,8 @@ class ParameterServer:
                 if r == self.rank and int(s) in self.state:
                     m, v = self.state[int(s)]
                     m.copy_(torch.from_numpy(z[f"m{s}"]))
-                    v.copy_(torch.from_numpy(z[f"v{s}"]))
+                    if v.numel():
+                        v.copy_(torch.from_numpy(z[f"v{s}"]))
             if r == self.rank:
                 self.t = int(h["t"])
         torch.cuda.synchronize()
@@ -553,5 +564,5 @@ class ParameterServer:
         """(4W + 8) n for SGD, (4W + 24) n for Adam, summed over local slices.
         (Two-level aggregation moves more local bytes -- the partial sum is written and re-read --
         but the algorithmic figure is the same: W gradients in, one update out.)"""
-        k = 4 * self.plan.W + (24 if self.optimizer == "adam" else 8)
+        k = 4 * self.plan.W + {"adam": 24, "momentum": 16}.get(self.optimizer, 8)
         return sum(k * (L.end - L.begin) for L in self.plan.launches)

@@ -272,3 +272,45 @@ def test_checkpoint_resume_continues_bit_exactly(tmp_path):
         c.load(str(tmp_path))  # a different shard map is refused
     for x in (a, b, c):
         x.close()
+
+
+@pytest.mark.parametrize("W,n", [(1, 5), (4, 4099), (6, 300_001)])
+def test_momentum_bit_exact(oracle, W, n):
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    acc = np.zeros(n, np.float32)
+    dp, da = dev(p), dev(acc)
+    dg = [torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(W)]
+    for t in (1, 2, 3, 4):
+        grads = [oracle.fill_uniform(n, 2, t, w, threads=4) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(dg[w], 2, t, w)
+        K.dense_apply_momentum(dp, da, dg, 0.05, 0.9)
+        oracle.dense_momentum(p, acc, grads, 0.05, 0.9, threads=4)
+    assert same(dp, p) and same(da, acc)
+
+
+def test_parameter_server_momentum_with_checkpoint(oracle, tmp_path):
+    sizes, S, W = [50_000, 3, 7_000], 2, 3
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer="momentum", lr=0.05, momentum=0.9)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp, ha = oracle.fill_uniform(P, 1, 0, 0), np.zeros(P, np.float32)
+    for t in (1, 2, 3):
+        hg = [oracle.fill_uniform(P, 2, t, w) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(ps.grad_buffer(w), 2, t, w)
+        ps.step()
+        oracle.dense_momentum(hp, ha, hg, 0.05, 0.9)
+        if t == 2:
+            ps.save(str(tmp_path))
+    for s, x in ps.dump().items():
+        b, e = x["range"]
+        assert same(torch.from_numpy(x["p"]), hp[b:e]) and same(torch.from_numpy(x["m"]), ha[b:e]) and "v" not in x
+    q = b200ps.ParameterServer(sizes, S, W, optimizer="momentum", lr=0.05, momentum=0.9)
+    q.load(str(tmp_path))
+    for w in range(W):
+        K.fill_uniform(q.grad_buffer(w), 2, 3, w)
+    q.step()
+    assert torch.equal(q.replica, ps.replica)
+    ps.close()
+    q.close()

@@ -160,3 +160,23 @@ def test_long_segment_chunked_fold(oracle, nporacle):
     assert np.array_equal(a, b)
     naive = t0[7].astype(np.float64) - 0.5 * 0.125 * grad[ids == 7].astype(np.float64).sum(0)
     assert np.allclose(a[7], naive, rtol=1e-4, atol=1e-5)
+
+
+def test_momentum_kat_and_c_vs_numpy(oracle, nporacle):
+    """TF ApplyMomentum: accum = momentum*accum + g; p -= lr*accum.  p=1, g=2, lr=.5, momentum=.5:
+    step 1 accum 2 -> p 0; step 2 accum 3 -> p -1.5 (all exact in binary)."""
+    p, acc = np.array([1.0], np.float32), np.zeros(1, np.float32)
+    g = [np.array([2.0], np.float32)]
+    oracle.dense_momentum(p, acc, g, 0.5, 0.5)
+    assert (p[0], acc[0]) == (0.0, 2.0)
+    oracle.dense_momentum(p, acc, g, 0.5, 0.5)
+    assert (p[0], acc[0]) == (-1.5, 3.0)
+    n, W = 2777, 5
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    a = np.zeros(n, np.float32)
+    q, b = p.copy(), a.copy()
+    for t in (1, 2, 3):
+        gs = [oracle.fill_uniform(n, 2, t, w) for w in range(W)]
+        oracle.dense_momentum(p, a, gs, 0.05, 0.9, threads=3)
+        q, b = nporacle.dense_momentum(q, b, gs, 0.05, 0.9)
+    assert np.array_equal(p, q) and np.array_equal(a, b)
