@@ -276,6 +276,42 @@ class EmbeddingTable:
         torch.cuda.synchronize()
         return {s: (self.lay.shard_range[s], self.shards[s].cpu().numpy()) for s in self.local_shards}
 
+    # ---- checkpoint / resume of the table shards ---------------------------
+    def save(self, directory: str):
+        """Every rank writes its shards (and Adagrad accumulators) with the row partition as header:
+        <directory>/table-rank<r>-of-<G>.npz."""
+        import json
+        import os
+
+        os.makedirs(directory, exist_ok=True)
+        self.check_barriers()
+        torch.cuda.synchronize()
+        L = self.lay
+        header = {"format": "b200ps-table-1", "rows": L.rows, "dim": L.dim, "shards": L.S, "optimizer": self.optimizer,
+                  "rank": self.rank, "world": self.world, "ranges": {str(s): list(L.shard_range[s]) for s in self.local_shards}}
+        arrays = {"header": np.frombuffer(json.dumps(header).encode(), dtype=np.uint8)}
+        for s in self.local_shards:
+            arrays[f"rows{s}"] = self.shards[s].cpu().numpy()
+            if L.adagrad:
+                arrays[f"accum{s}"] = self.accums[s].cpu().numpy()
+        np.savez(os.path.join(directory, f"table-rank{self.rank}-of-{self.world}.npz"), **arrays)
+
+    def load(self, directory: str):
+        """Restores this rank's shards from a checkpoint written with the same geometry and world size."""
+        import json
+        import os
+
+        z = np.load(os.path.join(directory, f"table-rank{self.rank}-of-{self.world}.npz"))
+        h = json.loads(bytes(z["header"]).decode())
+        L = self.lay
+        if (h["rows"], h["dim"], h["shards"], h["optimizer"], h["world"]) != (L.rows, L.dim, L.S, self.optimizer, self.world):
+            raise ValueError(f"table checkpoint was written for a different geometry: {h}")
+        for s in self.local_shards:
+            self.shards[s].copy_(torch.from_numpy(z[f"rows{s}"]))
+            if L.adagrad:
+                self.accums[s].copy_(torch.from_numpy(z[f"accum{s}"]))
+        torch.cuda.synchronize()
+
     def bytes_per_step(self, n_unique_local: int) -> Dict[str, int]:
         """Algorithmic bytes: gather B*(8 + 2*4*dim) per worker; push B*(8 + 4*dim) per
         entry kept + unique * 8*dim (SGD) or 16*dim (Adagrad)."""

@@ -290,3 +290,33 @@ def test_serve_and_route_with_emulated_ranks(oracle, dim, world):
     oracle.sparse_apply_sgd(table, 0, np.ascontiguousarray(grad.reshape(-1, dim)[keep]), ids.reshape(-1)[keep],
                             np.float32(1.0) / np.float32(W), np.float32(0.05))
     assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
+
+
+def test_embedding_table_checkpoint_resume(tmp_path):
+    """save -> new table -> load -> one more push equals the uninterrupted run (rows and accumulators)."""
+    rows, dim, S, W, B = 9_000, 16, 3, 2, 500
+
+    def feed(tab, step):
+        ids = b200ps.synth.make_ids("uniform", rows, W, B, step)
+        for w in range(W):
+            tab.ids[w].copy_(torch.from_numpy(ids[w]))
+            K.fill_uniform(tab.grad_rows[w].view(-1), 2, step, w)
+
+    a = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="adagrad")
+    a.init_uniform(1)
+    feed(a, 1)
+    a.push_step()
+    a.save(str(tmp_path))
+    feed(a, 2)
+    a.push_step()
+    b = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="adagrad")
+    b.load(str(tmp_path))
+    feed(b, 2)
+    b.push_step()
+    for s in range(S):
+        assert torch.equal(a.shards[s], b.shards[s]) and torch.equal(a.accums[s], b.accums[s])
+    c = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd")
+    with pytest.raises(ValueError):
+        c.load(str(tmp_path))
+    for t in (a, b, c):
+        t.close()
