@@ -423,6 +423,28 @@ class ParameterServer:
             self._events = {k: [] for k in self._events}
         return out
 
+    def step_async_ordered(self):
+        """A reproducible stand-in for TensorFlow's default ASYNCHRONOUS PS training (SURVEY.md 8(f)
+        rank 4): every worker's gradient is applied on its own, one after the other in worker order
+        (no averaging), so W optimizer steps happen per call and the result does not depend on
+        timing.  True asynchrony cannot be parity-checked; this fixed round-robin can.  "flat"
+        aggregation only (each launch folds exactly one worker's buffer)."""
+        if self.plan.two_level or self.transport == "nccl":
+            raise ValueError("step_async_ordered needs aggregate='flat' and transport='peer'")
+        self._barrier()
+        inv_w, self.inv_w = self.inv_w, 1.0
+        try:
+            for w in range(self.plan.W):
+                self.t += 1
+                a = self._opt_scalars()
+                for L in self.plan.launches:
+                    if L.end > L.begin:
+                        one = Launch(L.shard, L.begin, L.end, [L.grad_src[w]], L.mirror_ranks if w == self.plan.W - 1 else [])
+                        self._launch(one, L.begin, L.end, a)
+        finally:
+            self.inv_w = inv_w
+        self._barrier()
+
     def _step_nccl(self, a):
         import torch.distributed as dist
 

@@ -314,3 +314,28 @@ def test_parameter_server_momentum_with_checkpoint(oracle, tmp_path):
     assert torch.equal(q.replica, ps.replica)
     ps.close()
     q.close()
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+def test_ordered_async_mode(oracle, opt):
+    """Fixed round-robin 'asynchronous' mode: each worker's gradient applied on its own, in worker
+    order -- W optimizer steps per call, bit-identical to the same loop on the oracle."""
+    sizes, S, W = [30_000, 5, 4_000], 2, 3
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, lr=1e-3 if opt == "adam" else 0.05)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp, hm, hv = oracle.fill_uniform(P, 1, 0, 0), np.zeros(P, np.float32), np.zeros(P, np.float32)
+    t = 0
+    for step in (1, 2):
+        hg = [oracle.fill_uniform(P, 2, step, w) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(ps.grad_buffer(w), 2, step, w)
+        ps.step_async_ordered()
+        for w in range(W):
+            t += 1
+            if opt == "adam":
+                oracle.dense_adam(hp, hm, hv, [hg[w]], oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t))
+            else:
+                oracle.dense_sgd(hp, [hg[w]], 0.05)
+    assert ps.t == t and same(ps.replica, hp)
+    ps.close()
