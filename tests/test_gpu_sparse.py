@@ -188,6 +188,45 @@ def test_c2_shapes_full_batch(oracle):
     assert np.array_equal(dt.cpu().numpy().view(np.uint32), table.view(np.uint32))
 
 
+@pytest.mark.parametrize("kind", ["uniform", "zipf"])
+def test_c2_at_baseline_size(oracle, kind):
+    """BASELINE configs[2] at its real size -- 10 M x 64 table over 8 PS shards, 8 workers, 262 144
+    ids per worker per step, the ids bench.py uses (synth.make_ids) -- one pull and one push:
+    every integer of the plan, the pulled rows of a worker and the whole updated table are
+    bit-exact against the oracle."""
+    from b200ps import synth
+
+    rows, S, dim, W, B = 10_000_000, 8, 64, 8, 262_144
+    ids = synth.make_ids(kind, rows, W, B, 1)
+    flat = ids.reshape(-1)
+    geom = K.table_geom(rows, dim, S)
+    dids = [dev(ids[w]) for w in range(W)]
+    nt = min(16, len(__import__("os").sched_getaffinity(0)))
+    table = oracle.fill_uniform(rows * dim, 1, 0, 0, threads=nt).reshape(rows, dim)
+    dt = K.fill_uniform(torch.empty(rows * dim, dtype=torch.float32, device="cuda"), 1, 0, 0).view(rows, dim)
+    shards = shard_views(dt, rows, S)
+    # pull (a10): worker 3's rows
+    out = torch.empty(B, dim, dtype=torch.float32, device="cuda")
+    K.sparse_gather(out, shards, geom, dids[3])
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.gather(table, ids[3]).view(np.uint32))
+    # push (a11): the plan
+    ws = K.sparse_workspace(W * B, dim)
+    K.sparse_sort_segment(dids, B, geom, ws)
+    plan = K.sparse_plan_read(ws, W * B, rows)
+    s, perm, seg, uniq, off = oracle.sort_segment(flat)
+    assert plan["n_kept"] == W * B and plan["n_bad"] == 0 and plan["n_unique"] == len(uniq)
+    assert np.array_equal(plan["sorted_ids"], s) and np.array_equal(plan["perm"], perm)
+    assert np.array_equal(plan["seg_id"], seg) and np.array_equal(plan["unique_ids"], uniq)
+    assert np.array_equal(plan["seg_offset"], off)
+    # push (a12): the updated table
+    grad = oracle.fill_uniform(W * B * dim, 2, 1, 0, threads=nt).reshape(W * B, dim)
+    dg = K.fill_uniform(torch.empty(W * B * dim, dtype=torch.float32, device="cuda"), 2, 1, 0).view(W, B, dim)
+    K.sparse_apply_sgd(shards, [dg[w] for w in range(W)], B, geom, 0.05, ws)
+    oracle.sparse_apply_sgd(table, 0, grad, flat, np.float32(1.0) / np.float32(W), np.float32(0.05))
+    got = dt.cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), table.view(np.uint32))
+
+
 @pytest.mark.parametrize("opt,kind", [("sgd", "zipf"), ("adagrad", "uniform")])
 def test_embedding_table_host_api(oracle, opt, kind):
     """b200ps.EmbeddingTable (world = 1): pull then push for 2 steps equals the oracle bit for bit."""

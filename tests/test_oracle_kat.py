@@ -180,3 +180,35 @@ def test_momentum_kat_and_c_vs_numpy(oracle, nporacle):
         oracle.dense_momentum(p, a, gs, 0.05, 0.9, threads=3)
         q, b = nporacle.dense_momentum(q, b, gs, 0.05, 0.9)
     assert np.array_equal(p, q) and np.array_equal(a, b)
+
+
+def test_chunked_fold_of_a_130k_entry_hot_row_against_the_plain_left_fold(oracle):
+    """SURVEY 8(a) a12 wrote "sum in sorted order"; the oracle folds a segment longer than 256
+    entries chunk-wise (256-entry chunks left to right, then the chunk sums left to right).  For the
+    hottest id of C2 under Zipf(1.05) -- 130 108 entries -- this measures what that changes.
+
+    No two fp32 summation orders of 130 k values of magnitude <= 1 agree to 1e-6 relative: the plain
+    left fold is itself ~1.6e-5 (absolute, in the updated parameter) from the exact sum, because every
+    add rounds a partial sum of magnitude up to ~400.  So the pin is: (1) the chunked result is at
+    least as close to the exact (float64) answer as the plain left fold is, (2) the two differ by less
+    than the plain fold's own rounding-error bound, and (3) up to 256 entries the two are the same bits."""
+    n, dim = 130_108, 64
+    g = oracle.fill_uniform(n * dim, 2, 1, 0, threads=4).reshape(n, dim)
+    t0 = oracle.fill_uniform(dim, 1, 0, 0).reshape(1, dim)
+    inv_w, lr = np.float32(1.0) / np.float32(8), np.float32(0.05)
+    chunked = oracle.sparse_apply_sgd(t0.copy(), 0, g, np.zeros(n, np.int64), inv_w, lr)[0]
+    plain_sum = np.cumsum(g, axis=0, dtype=np.float32)[-1]  # cumsum is the sequential left fold
+    plain = t0[0] - lr * (plain_sum * inv_w)
+    exact = t0[0].astype(np.float64) - 0.05 * (g.astype(np.float64).sum(0) / 8.0)
+    err_chunked, err_plain = np.abs(chunked - exact).max(), np.abs(plain - exact).max()
+    assert err_chunked <= err_plain                      # measured: 1.7e-6 vs 1.6e-5
+    assert err_chunked <= 4e-6
+    # standard bound for recursive summation: n * u * max|partial sum|, scaled by lr / W
+    bound = n * 2.0 ** -24 * np.abs(np.cumsum(g, axis=0, dtype=np.float64)).max() * 0.05 / 8.0
+    assert np.abs(chunked - plain).max() <= bound        # measured 1.7e-5, bound ~2e-2
+    assert np.abs(chunked - plain).max() <= 5e-5
+    # (3) a segment of exactly 256 entries is the plain left fold, bit for bit
+    k = 256
+    c = oracle.sparse_apply_sgd(t0.copy(), 0, g[:k].copy(), np.zeros(k, np.int64), inv_w, lr)[0]
+    q = t0[0] - lr * (np.cumsum(g[:k], axis=0, dtype=np.float32)[-1] * inv_w)
+    assert np.array_equal(c.view(np.uint32), q.view(np.uint32))
