@@ -426,11 +426,9 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    if os.environ.get("B200PS_DENSE_TUNING"):  # "threads,ctas_per_sm,unroll" -- for geometry experiments
-        K.set_dense_tuning(*[int(x) for x in os.environ["B200PS_DENSE_TUNING"].split(",")])
     label, sizes, S, W, opt = workload(args.workload, world)
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
-                                aggregate=args.aggregate, barrier=args.barrier, overlap=args.overlap)
+                                aggregate=args.aggregate, overlap=args.overlap)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)

@@ -139,6 +139,13 @@ int b200ps_dense_apply_adam(float* d_params, float* d_m, float* d_v, const float
 int b200ps_dense_apply_momentum(float* d_params, float* d_accum, const float* const* d_grads, int W,
                                 uint64_t n, float inv_w, float lr, float momentum,
                                 float* const* d_mirrors, int n_mirrors, void* stream);
+/* TensorFlow's ApplyFtrl with lr_power = -0.5 (the "wide" part of Wide&Deep):
+ *   na = accum + g*g;  sigma = (sqrt(na) - sqrt(accum)) / lr;  linear += g - sigma*p;
+ *   p = |linear| > l1 ? (sign(linear)*l1 - linear) / (sqrt(na)/lr + 2*l2) : 0;  accum = na
+ * accum starts at 0.1 (TF's initial_accumulator_value), linear at 0. */
+int b200ps_dense_apply_ftrl(float* d_params, float* d_accum, float* d_linear, const float* const* d_grads,
+                            int W, uint64_t n, float inv_w, float lr, float l1, float l2,
+                            float* const* d_mirrors, int n_mirrors, void* stream);
 /* d_out[i] = ((b_0[i] + b_1[i]) + b_2[i]) + ...  -- the local half of the two-level aggregation:
  * a GPU that hosts several workers folds their gradients once (in worker order), and only that
  * partial sum crosses NVLink; the owning shard then folds the G partials in GPU order. */
@@ -293,6 +300,150 @@ int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total, uint64_t 
 int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const int64_t* const* d_ids,
                                    const float* const* d_grad_rows, int W, uint64_t ids_per_worker,
                                    const b200ps_table_geom_t* geom, float lr, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Context group: the PS tasks and compute-task buffers of ONE GPU as one object the library owns
+ * (SURVEY.md 8(b) "dense group").  Reference: none -- this is the part of TensorFlow's PS runtime
+ * that holds the variables, their optimizer slots and the transport between the PS and WORKER
+ * tasks of k8s-operator.md:6; a Go operator replacing pkg/trainer/replicas.go (images/tf3.PNG)
+ * would bind exactly these calls through cgo.
+ *
+ * One process per GPU drives one context ("rank" r of "world" G, with the CUDA device it runs on
+ * current on the calling thread).  Placement is b200ps_placement_gpu: shard s -> GPU s mod G,
+ * compute task w -> GPU w mod G.  The context owns, in device memory:
+ *   - one arena, exported to the other ranks of the box (CUDA IPC):
+ *       [ replica: P_pad fp32 | (two-level, G > 1: this GPU's partial sum: P_pad) |
+ *         one gradient buffer of P_pad per local compute task | barrier + slice-ready flags ]
+ *   - the optimizer state (Adam m, v; momentum accumulator; FTRL accum, linear) of its shards,
+ *   - the Adam step counter and the launch plan.
+ * The master copy of slice s is the slice-s range of its owner's replica; the step kernel writes
+ * the updated slice into every other rank's replica (pull fused into the step).
+ *
+ * Set-up sequence for G > 1 (the caller moves the 64-byte handles over any host channel and
+ * provides ONE host-side barrier; the library calls nothing back):
+ *     b200ps_ctx_create -> b200ps_ctx_export_handle -> (all-gather the handles) ->
+ *     b200ps_ctx_import_handles -> (host barrier: every rank has imported) -> steps ...
+ *     -> (host barrier: nobody is inside a step) -> b200ps_ctx_destroy
+ * All ranks must issue the same sequence of collective calls (b200ps_dense_step,
+ * b200ps_dense_step_async_ordered, b200ps_dense_step_host): each one contains stream-ordered
+ * barriers through peer memory.  A rank that never arrives makes the others' barrier time out
+ * (~4 s); from then on every kernel of the context is a no-op and every call returns
+ * B200PS_ERR_STATE -- parameters are never updated from gradients that were not all there.
+ *
+ * Calls take the stream the work is ordered on.  A context is driven by one host thread.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200ps_ctx b200ps_ctx_t;
+
+enum { B200PS_OPT_SGD = 0, B200PS_OPT_ADAM = 1, B200PS_OPT_MOMENTUM = 2, B200PS_OPT_FTRL = 3 };
+enum { B200PS_AGG_FLAT = 0,      /* g = (1/W) * left fold over the workers in worker order (a6) */
+       B200PS_AGG_TWO_LEVEL = 1, /* G > 1: every GPU folds its own workers (worker order), the owner
+                                    folds the per-GPU partial sums in GPU order; same bits as FLAT on one GPU */
+       B200PS_AGG_MULTIMEM = 2   /* G > 1: as TWO_LEVEL, but the G partial sums are added inside the
+                                    NVSwitch (multimem.ld_reduce) -- the switch's summation order, so
+                                    results match the oracle to 1e-6 relative, not bit for bit.  Needs
+                                    multicast support (b200ps_multicast_supported). */ };
+
+typedef struct {
+    int optimizer;       /* B200PS_OPT_* */
+    int aggregate;       /* B200PS_AGG_* */
+    double lr;           /* all optimizers */
+    double beta1, beta2, eps; /* Adam (TF formulation) */
+    double momentum;     /* ApplyMomentum */
+    double ftrl_l1, ftrl_l2, ftrl_accum_init; /* ApplyFtrl with lr_power = -0.5 */
+    int threads, ctas_per_sm, unroll; /* launch geometry of this context's dense kernels; 0 = default */
+    int use_graph;       /* 1: b200ps_dense_step replays one CUDA graph per step (captured on first use) */
+    int pipeline_folds;  /* G > 1, two-level: slice-wise fold that signals the slice owners, overlapping
+                            the NVLink exchange with the local folds */
+    uint64_t host_chunk_elems; /* pipelining granularity of b200ps_dense_step_host; 0 = 4 Mi elements */
+} b200ps_dense_options_t;
+
+/* fills *opt with the defaults: SGD, lr 0.01; Adam 1e-3 / 0.9 / 0.999 / 1e-8; momentum 0.9;
+ * FTRL l1 = l2 = 0, accumulator 0.1; TWO_LEVEL aggregation; no graph. */
+int b200ps_dense_options_default(b200ps_dense_options_t* opt);
+
+/* S = b200ps_cluster_num_shards(cluster) must equal the map's shard count; W = the cluster's
+ * compute tasks.  Allocates the arena and the state on the current device. */
+int b200ps_ctx_create(const b200ps_cluster_t* cluster, const b200ps_shardmap_t* map, int rank, int world,
+                      const b200ps_dense_options_t* opt, b200ps_ctx_t** out);
+int b200ps_ctx_destroy(b200ps_ctx_t* ctx);
+int b200ps_ctx_export_handle(b200ps_ctx_t* ctx, void* handle_out /* B200PS_IPC_HANDLE_BYTES */);
+/* handles: world * B200PS_IPC_HANDLE_BYTES bytes, rank-major (this rank's own entry is ignored) */
+int b200ps_ctx_import_handles(b200ps_ctx_t* ctx, const void* handles);
+/* joins `stream` and the context's own copy streams, then reports a barrier time-out if one occurred */
+int b200ps_ctx_sync(b200ps_ctx_t* ctx, void* stream);
+
+/* The launch plan of one rank, pure host arithmetic (no device needed): what b200ps_ctx_create lays
+ * out and what b200ps_dense_step executes. */
+typedef struct b200ps_plan b200ps_plan_t;
+int b200ps_plan_build(const b200ps_shardmap_t* map, int num_workers, int rank, int world, int aggregate,
+                      b200ps_plan_t** out);
+void b200ps_plan_destroy(b200ps_plan_t* plan);
+uint64_t b200ps_plan_params_padded(const b200ps_plan_t* plan);          /* P_pad */
+int b200ps_plan_two_level(const b200ps_plan_t* plan);                   /* 1 if per-GPU partial sums are used */
+int b200ps_plan_first_grad_slot(const b200ps_plan_t* plan);             /* arena slot (units of P_pad) of the first gradient buffer */
+uint64_t b200ps_plan_arena_elems(const b200ps_plan_t* plan, int of_rank); /* fp32 elements before the flag words */
+int b200ps_plan_num_local_workers(const b200ps_plan_t* plan);
+int b200ps_plan_local_worker(const b200ps_plan_t* plan, int i);         /* compute-task rank of the i-th local one */
+int b200ps_plan_grad_offset(const b200ps_plan_t* plan, int worker, int* rank, uint64_t* offset);
+int b200ps_plan_num_launches(const b200ps_plan_t* plan);                /* = local shards */
+/* launch i: its shard and slice, the buffers it folds in fold order (rank, arena offset in elements;
+ * arrays of B200PS_MAX_WORKERS) and the ranks whose replica it mirrors into (B200PS_MAX_MIRRORS).
+ * Any output may be NULL. */
+int b200ps_plan_launch(const b200ps_plan_t* plan, int i, int* shard, uint64_t* begin, uint64_t* end, int* n_src,
+                       int* src_rank, uint64_t* src_offset, int* n_mirrors, int* mirror_rank);
+const b200ps_plan_t* b200ps_ctx_plan(const b200ps_ctx_t* ctx);          /* owned by the context */
+uint64_t b200ps_ctx_step_count(const b200ps_ctx_t* ctx);               /* optimizer steps taken (Adam's t) */
+/* (4W + 8) n for SGD, (4W + 24) n for Adam and FTRL, (4W + 16) n momentum, summed over local slices */
+uint64_t b200ps_ctx_algorithmic_bytes_per_step(const b200ps_ctx_t* ctx);
+
+/* ---- parameters ---- */
+int b200ps_dense_init(b200ps_ctx_t* ctx, const float* h_params /* P_pad */, void* stream); /* resets state and t */
+int b200ps_dense_init_uniform(b200ps_ctx_t* ctx, uint64_t seed, void* stream);           /* p[i] = u(seed,0,0,i) */
+/* device views (valid until destroy): the replica, a local compute task's gradient buffer (zero-copy
+ * push: the worker's kernels write here), the state of a local shard (second is NULL if unused) */
+int b200ps_dense_replica(b200ps_ctx_t* ctx, float** d_params);
+int b200ps_dense_grad_buffer(b200ps_ctx_t* ctx, int worker, float** d_grad);
+/* base of rank r's arena as mapped in this process (r = own rank: the local arena) -- for probes and
+ * for workers that read a peer's replica or write a peer's gradient buffer directly */
+int b200ps_ctx_arena_base(b200ps_ctx_t* ctx, int of_rank, float** d_base);
+int b200ps_dense_state(b200ps_ctx_t* ctx, int shard, float** d_first, float** d_second, uint64_t* n);
+
+/* ---- the step ---- */
+/* push (H2D of one local compute task's gradient) / pull (D2H of the replica); asynchronous */
+int b200ps_dense_push(b200ps_ctx_t* ctx, int worker, const float* h_grad, void* stream);
+int b200ps_dense_pull(b200ps_ctx_t* ctx, int worker, float* h_params, void* stream);
+/* push + aggregate + apply + pull for every local shard; gradients are already in the grad buffers */
+int b200ps_dense_step(b200ps_ctx_t* ctx, void* stream);
+/* a reproducible stand-in for asynchronous PS training: every worker's gradient
+ * applied on its own, in worker order, no averaging -- W optimizer steps per call.  FLAT only. */
+int b200ps_dense_step_async_ordered(b200ps_ctx_t* ctx, void* stream);
+/* a whole step with HOST buffers, pipelined chunk by chunk over the context's copy streams:
+ * h_grads[i] = gradient (P_pad floats, pinned) of the i-th local compute task; h_params_out (may be
+ * NULL) receives the updated replica.  The copy-out of one step overlaps the copy-in of the next:
+ * call b200ps_dense_host_sync before reading h_params_out. */
+int b200ps_dense_step_host(b200ps_ctx_t* ctx, const float* const* h_grads, float* h_params_out, void* stream);
+int b200ps_dense_host_sync(b200ps_ctx_t* ctx);
+
+/* ---- inspection, checkpoint / resume ("storage" is a goal, k8s-operator.md:2) ---- */
+/* h_params: the whole replica (P_pad); h_first / h_second (may be NULL): P_pad floats each, only the
+ * ranges of this rank's shards are written.  Synchronises. */
+int b200ps_dense_dump(b200ps_ctx_t* ctx, float* h_params, float* h_first, float* h_second, void* stream);
+/* <directory>/ps-rank<r>-of-<G>.b200ps: this rank's shards (parameters, state), step counter and the
+ * shard-map header; written to a temporary file and renamed.  Every rank calls save; put a host
+ * barrier between the ranks' save and a later load (load reads every rank's file for the parameters). */
+int b200ps_dense_save(b200ps_ctx_t* ctx, const char* directory, void* stream);
+int b200ps_dense_load(b200ps_ctx_t* ctx, const char* directory, void* stream);
+
+/* ---- tuning / tracing ---- */
+int b200ps_ctx_set_tuning(b200ps_ctx_t* ctx, int threads, int ctas_per_sm, int unroll); /* 0 keeps a value */
+/* switches graph replay of b200ps_dense_step on or off (as the use_graph option does at creation) */
+int b200ps_ctx_set_graph(b200ps_ctx_t* ctx, int on);
+/* profile on: b200ps_dense_step brackets its phases with events (and does not replay a graph);
+ * b200ps_ctx_phase_ms returns the mean per step since the last call and resets (synchronises). */
+int b200ps_ctx_set_profile(b200ps_ctx_t* ctx, int on);
+int b200ps_ctx_phase_ms(b200ps_ctx_t* ctx, float* fold_ms, float* apply_ms, float* barrier_ms);
+/* 1 if the current device and driver support NVSwitch multicast objects (B200PS_AGG_MULTIMEM) */
+int b200ps_multicast_supported(void);
 
 #ifdef __cplusplus
 }

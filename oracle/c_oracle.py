@@ -48,6 +48,7 @@ def lib():
         L.ps_dense_sgd.argtypes = [vp, vp, i32, u64, f32, f32, i32]
         L.ps_dense_fold.argtypes = [vp, vp, i32, u64, i32]
         L.ps_dense_momentum.argtypes = [vp, vp, vp, i32, u64, f32, f32, f32, i32]
+        L.ps_dense_ftrl.argtypes = [vp, vp, vp, vp, i32, u64, f32, f32, f32, f32, i32]
         L.ps_adam_scalars.restype = AdamT
         L.ps_adam_scalars.argtypes = [C.c_double] * 4 + [u64]
         L.ps_dense_adam.argtypes = [vp, vp, vp, vp, i32, u64, f32, C.POINTER(AdamT), i32]
@@ -135,6 +136,13 @@ def dense_momentum(p, accum, grads, lr, momentum, threads=1, inv_w=None):
     inv_w = np.float32(1.0) / np.float32(len(grads)) if inv_w is None else np.float32(inv_w)
     lib().ps_dense_momentum(_p(p), _p(accum), C.addressof(gp), len(grads), p.size, inv_w, lr, momentum, threads)
     return p, accum
+
+
+def dense_ftrl(p, accum, linear, grads, lr, l1, l2, threads=1, inv_w=None):
+    gp = _gradptrs(grads)
+    inv_w = np.float32(1.0) / np.float32(len(grads)) if inv_w is None else np.float32(inv_w)
+    lib().ps_dense_ftrl(_p(p), _p(accum), _p(linear), C.addressof(gp), len(grads), p.size, inv_w, lr, l1, l2, threads)
+    return p, accum, linear
 
 
 def adam_scalars(lr, beta1, beta2, eps, t) -> AdamT:

@@ -84,6 +84,21 @@ def dense_momentum(p, accum, grads, lr, momentum, inv_w=None):
     return p - np.float32(lr) * a2, a2
 
 
+def dense_ftrl(p, accum, linear, grads, lr, l1, l2, inv_w=None):
+    """TF ApplyFtrl, lr_power = -0.5 (same operation order as ps_dense_ftrl)."""
+    f = np.float32
+    g = aggregate(grads, f(1.0) / f(len(grads)) if inv_w is None else inv_w)
+    lr, l1, two_l2 = f(lr), f(l1), f(2.0) * f(l2)
+    na = accum + g * g
+    sn = np.sqrt(na)
+    sigma = (sn - np.sqrt(accum)) / lr
+    li = linear + (g - sigma * p)
+    x = np.where(li > 0, l1, np.where(li < 0, -l1, f(0))).astype(f) - li
+    y = sn / lr + two_l2
+    p2 = np.where(np.abs(li) > l1, x / y, f(0)).astype(f)
+    return p2, na.astype(f), li.astype(f)
+
+
 def adam_scalars(lr: float, beta1: float, beta2: float, eps: float, t: int):
     lr_t = np.float32(lr * np.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t))
     return dict(lr_t=lr_t, beta1=np.float32(beta1), beta2=np.float32(beta2),

@@ -139,6 +139,40 @@ void ps_dense_momentum(float* p, float* accum, const float* const* grads, int W,
     }
 }
 
+/* TensorFlow's ApplyFtrl with lr_power = -0.5 (training_ops: FtrlCompute), one rounding per operation:
+ *   na = accum + g*g;  sigma = (sqrt(na) - sqrt(accum)) / lr;  linear = linear + (g - sigma*p);
+ *   x = sign(linear)*l1 - linear;  y = sqrt(na)/lr + 2*l2;  p = |linear| > l1 ? x/y : 0;  accum = na */
+void ps_dense_ftrl(float* p, float* accum, float* linear, const float* const* grads, int W, uint64_t n, float inv_w,
+                   float lr, float l1, float l2, int threads) {
+    int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;
+    const float two_l2 = 2.0f * l2;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
+    for (b = 0; b < nb; ++b) {
+        float acc[BLK];
+        uint64_t i0 = (uint64_t)b * BLK, len = n - i0 < BLK ? n - i0 : BLK, i;
+        int w;
+        for (i = 0; i < len; ++i) acc[i] = grads[0][i0 + i];
+        for (w = 1; w < W; ++w) {
+            const float* g = grads[w] + i0;
+            for (i = 0; i < len; ++i) acc[i] = acc[i] + g[i];
+        }
+        for (i = 0; i < len; ++i) {
+            float g = acc[i] * inv_w;
+            float a = accum[i0 + i], na = a + g * g;
+            float sn = sqrtf(na);
+            float sigma = (sn - sqrtf(a)) / lr;
+            float sp = sigma * p[i0 + i];
+            float li = linear[i0 + i] + (g - sp);
+            float sgn = li > 0.f ? l1 : (li < 0.f ? -l1 : 0.f);
+            float x = sgn - li;
+            float y = sn / lr + two_l2;
+            linear[i0 + i] = li;
+            p[i0 + i] = fabsf(li) > l1 ? x / y : 0.f;
+            accum[i0 + i] = na;
+        }
+    }
+}
+
 void ps_dense_fold(float* dst, const float* const* bufs, int W, uint64_t n, int threads) {
     /* the local half of the two-level aggregation: dst = ((b0 + b1) + b2) + ..., no scaling */
     int64_t nb = (int64_t)((n + BLK - 1) / BLK), b;

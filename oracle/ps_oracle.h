@@ -48,6 +48,9 @@ void ps_dense_sgd(float* p, const float* const* grads, int W, uint64_t n, float 
 /* TF ApplyMomentum (no Nesterov): accum = momentum*accum + g;  p -= lr*accum */
 void ps_dense_momentum(float* p, float* accum, const float* const* grads, int W, uint64_t n, float inv_w, float lr,
                        float momentum, int threads);
+/* TF ApplyFtrl, lr_power = -0.5 (accum starts at 0.1, linear at 0); see ps_oracle.c for the operation order */
+void ps_dense_ftrl(float* p, float* accum, float* linear, const float* const* grads, int W, uint64_t n, float inv_w,
+                   float lr, float l1, float l2, int threads);
 /* dst = ((b0 + b1) + b2) + ... (two-level aggregation: the per-GPU partial sum; the partials are
  * then folded in GPU order by ps_dense_* with inv_w = 1 / total workers) */
 void ps_dense_fold(float* dst, const float* const* bufs, int W, uint64_t n, int threads);

@@ -28,6 +28,17 @@ class AdamScalars(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("lr_t", "beta1", "beta2", "omb1", "omb2", "eps")]
 
 
+class DenseOptions(C.Structure):
+    """b200ps_dense_options_t"""
+    _fields_ = [("optimizer", C.c_int), ("aggregate", C.c_int), ("lr", C.c_double), ("beta1", C.c_double),
+                ("beta2", C.c_double), ("eps", C.c_double), ("momentum", C.c_double), ("ftrl_l1", C.c_double),
+                ("ftrl_l2", C.c_double), ("ftrl_accum_init", C.c_double), ("threads", C.c_int), ("ctas_per_sm", C.c_int),
+                ("unroll", C.c_int), ("use_graph", C.c_int), ("pipeline_folds", C.c_int), ("host_chunk_elems", C.c_uint64)]
+
+
+OPT_SGD, OPT_ADAM, OPT_MOMENTUM, OPT_FTRL = 0, 1, 2, 3
+AGG_FLAT, AGG_TWO_LEVEL, AGG_MULTIMEM = 0, 1, 2
+
 OK, ERR_INVALID, ERR_PARSE, ERR_VALIDATION, ERR_CUDA, ERR_RANGE, ERR_STATE = 0, -1, -2, -3, -4, -5, -6
 
 if not os.path.exists(LIB_PATH):
@@ -69,6 +80,7 @@ SIGNATURES = {
     "b200ps_dense_apply_adam": (_i32, [_vp, _vp, _vp, _vp, _i32, _u64, _f32, C.POINTER(AdamScalars), _vp, _i32, _vp]),
     "b200ps_dense_fold": (_i32, [_vp, _vp, _i32, _u64, _vp]),
     "b200ps_dense_apply_momentum": (_i32, [_vp, _vp, _vp, _i32, _u64, _f32, _f32, _f32, _vp, _i32, _vp]),
+    "b200ps_dense_apply_ftrl": (_i32, [_vp, _vp, _vp, _vp, _i32, _u64, _f32, _f32, _f32, _f32, _vp, _i32, _vp]),
     "b200ps_fill_uniform": (_i32, [_vp, _u64, _u64, _u64, _u64, _u64, _vp]),
     "b200ps_set_dense_tuning": (_i32, [_i32, _i32, _i32]),
     "b200ps_launch_count": (_u64, []),
@@ -93,6 +105,48 @@ SIGNATURES = {
     "b200ps_sparse_push_sgd_noalloc": (_i32, [_vp, _vp, _vp, _i32, _u64, C.POINTER(TableGeom), _f32, _vp]),
     "b200ps_sparse_plan_read": (_i32, [_vp, _u64, _u64, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64), _vp, _vp, _vp,
                                         _vp, _vp, _vp]),
+    # context group
+    "b200ps_dense_options_default": (_i32, [C.POINTER(DenseOptions)]),
+    "b200ps_ctx_create": (_i32, [_vp, _vp, _i32, _i32, C.POINTER(DenseOptions), _pp]),
+    "b200ps_ctx_destroy": (_i32, [_vp]),
+    "b200ps_ctx_export_handle": (_i32, [_vp, _vp]),
+    "b200ps_ctx_import_handles": (_i32, [_vp, _vp]),
+    "b200ps_ctx_sync": (_i32, [_vp, _vp]),
+    "b200ps_plan_build": (_i32, [_vp, _i32, _i32, _i32, _i32, _pp]),
+    "b200ps_plan_destroy": (None, [_vp]),
+    "b200ps_plan_params_padded": (_u64, [_vp]),
+    "b200ps_plan_two_level": (_i32, [_vp]),
+    "b200ps_plan_first_grad_slot": (_i32, [_vp]),
+    "b200ps_plan_arena_elems": (_u64, [_vp, _i32]),
+    "b200ps_plan_num_local_workers": (_i32, [_vp]),
+    "b200ps_plan_local_worker": (_i32, [_vp, _i32]),
+    "b200ps_plan_grad_offset": (_i32, [_vp, _i32, C.POINTER(_i32), C.POINTER(_u64)]),
+    "b200ps_plan_num_launches": (_i32, [_vp]),
+    "b200ps_plan_launch": (_i32, [_vp, _i32, C.POINTER(_i32), C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_i32), _vp, _vp,
+                                   C.POINTER(_i32), _vp]),
+    "b200ps_ctx_plan": (_vp, [_vp]),
+    "b200ps_ctx_step_count": (_u64, [_vp]),
+    "b200ps_ctx_algorithmic_bytes_per_step": (_u64, [_vp]),
+    "b200ps_dense_init": (_i32, [_vp, _vp, _vp]),
+    "b200ps_dense_init_uniform": (_i32, [_vp, _u64, _vp]),
+    "b200ps_dense_replica": (_i32, [_vp, _pp]),
+    "b200ps_dense_grad_buffer": (_i32, [_vp, _i32, _pp]),
+    "b200ps_ctx_arena_base": (_i32, [_vp, _i32, _pp]),
+    "b200ps_dense_state": (_i32, [_vp, _i32, _pp, _pp, C.POINTER(_u64)]),
+    "b200ps_dense_push": (_i32, [_vp, _i32, _vp, _vp]),
+    "b200ps_dense_pull": (_i32, [_vp, _i32, _vp, _vp]),
+    "b200ps_dense_step": (_i32, [_vp, _vp]),
+    "b200ps_dense_step_async_ordered": (_i32, [_vp, _vp]),
+    "b200ps_dense_step_host": (_i32, [_vp, _vp, _vp, _vp]),
+    "b200ps_dense_host_sync": (_i32, [_vp]),
+    "b200ps_dense_dump": (_i32, [_vp, _vp, _vp, _vp, _vp]),
+    "b200ps_dense_save": (_i32, [_vp, _cp, _vp]),
+    "b200ps_dense_load": (_i32, [_vp, _cp, _vp]),
+    "b200ps_ctx_set_tuning": (_i32, [_vp, _i32, _i32, _i32]),
+    "b200ps_ctx_set_graph": (_i32, [_vp, _i32]),
+    "b200ps_ctx_set_profile": (_i32, [_vp, _i32]),
+    "b200ps_ctx_phase_ms": (_i32, [_vp, C.POINTER(_f32), C.POINTER(_f32), C.POINTER(_f32)]),
+    "b200ps_multicast_supported": (_i32, []),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

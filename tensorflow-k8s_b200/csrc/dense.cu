@@ -23,9 +23,12 @@
 #include <atomic>
 #include <cmath>
 #include <cstdlib>
+#include <map>
+#include <mutex>
 
 #include "common.h"
 #include "cuda_util.h"
+#include "dense_internal.h"
 
 namespace b200ps {
 
@@ -33,9 +36,8 @@ std::atomic<uint64_t> g_launches{0};
 
 namespace {
 
-enum { OPT_SGD = 0, OPT_ADAM = 1, OPT_FOLD = 2, OPT_MOMENTUM = 3 };  // FOLD: p[i] = left fold of the buffers, nothing else
-#define HAS_M(OPT) ((OPT) == OPT_ADAM || (OPT) == OPT_MOMENTUM)  /* first state buffer: Adam's m / the momentum accumulator */
-#define HAS_V(OPT) ((OPT) == OPT_ADAM)
+#define HAS_M(OPT) ((OPT) == OPT_ADAM || (OPT) == OPT_MOMENTUM || (OPT) == OPT_FTRL)  /* first state buffer: Adam's m / momentum accumulator / FTRL accum */
+#define HAS_V(OPT) ((OPT) == OPT_ADAM || (OPT) == OPT_FTRL)  /* second: Adam's v / FTRL linear */
 
 struct DenseParams {
     const float* g[B200PS_MAX_WORKERS];
@@ -52,6 +54,7 @@ struct DenseParams {
     float beta1, beta2, omb1, omb2, eps;
     int load_kind;  // gradient loads: 0 = nc + L1 no-allocate + L2 evict-first, 1 = plain coherent ld.global
     int end_fence;  // 1: every thread ends with a system-scope fence (drains its peer stores inside the kernel)
+    const uint32_t* abort_word;  // non-null and *abort_word != 0: a barrier of this context timed out -> do nothing
 };
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -93,37 +96,47 @@ __device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
 
 // one element: g = inv_w * sum; optimizer update.  Same operation order as ps_dense_sgd / ps_dense_adam.
 template <int OPT>
-__device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const DenseParams& a) {
+__device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const DenseParams& a, const float lr) {
     if (OPT == OPT_FOLD) {
         p = sum;
         return;
     }
     const float g = __fmul_rn(sum, a.inv_w);
     if (OPT == OPT_SGD) {
-        p = __fsub_rn(p, __fmul_rn(a.lr, g));
+        p = __fsub_rn(p, __fmul_rn(lr, g));
     } else if (OPT == OPT_MOMENTUM) {  // TF ApplyMomentum: accum = momentum*accum + g; p -= lr*accum
         m = __fadd_rn(__fmul_rn(a.beta1, m), g);
-        p = __fsub_rn(p, __fmul_rn(a.lr, m));
+        p = __fsub_rn(p, __fmul_rn(lr, m));
+    } else if (OPT == OPT_FTRL) {
+        // TF ApplyFtrl, lr_power = -0.5 (m = accum, v = linear; beta1 = l1, beta2 = 2*l2); order as ps_dense_ftrl
+        const float na = __fadd_rn(m, __fmul_rn(g, g));
+        const float sn = __fsqrt_rn(na);
+        const float sigma = __fdiv_rn(__fsub_rn(sn, __fsqrt_rn(m)), lr);
+        v = __fadd_rn(v, __fsub_rn(g, __fmul_rn(sigma, p)));
+        const float x = __fsub_rn(v > 0.f ? a.beta1 : (v < 0.f ? -a.beta1 : 0.f), v);
+        const float y = __fadd_rn(__fdiv_rn(sn, lr), a.beta2);
+        p = fabsf(v) > a.beta1 ? __fdiv_rn(x, y) : 0.f;
+        m = na;
     } else {
         m = __fadd_rn(__fmul_rn(a.beta1, m), __fmul_rn(a.omb1, g));
         v = __fadd_rn(__fmul_rn(a.beta2, v), __fmul_rn(a.omb2, __fmul_rn(g, g)));
-        p = __fsub_rn(p, __fdiv_rn(__fmul_rn(a.lr, m), __fadd_rn(__fsqrt_rn(v), a.eps)));
+        p = __fsub_rn(p, __fdiv_rn(__fmul_rn(lr, m), __fadd_rn(__fsqrt_rn(v), a.eps)));
     }
 }
 
 template <int OPT>
-__device__ __forceinline__ void apply4(const float4& s, float4& p, float4& m, float4& v, const DenseParams& a) {
-    apply1<OPT>(s.x, p.x, m.x, v.x, a);
-    apply1<OPT>(s.y, p.y, m.y, v.y, a);
-    apply1<OPT>(s.z, p.z, m.z, v.z, a);
-    apply1<OPT>(s.w, p.w, m.w, v.w, a);
+__device__ __forceinline__ void apply4(const float4& s, float4& p, float4& m, float4& v, const DenseParams& a, const float lr) {
+    apply1<OPT>(s.x, p.x, m.x, v.x, a, lr);
+    apply1<OPT>(s.y, p.y, m.y, v.y, a, lr);
+    apply1<OPT>(s.z, p.z, m.z, v.z, a, lr);
+    apply1<OPT>(s.w, p.w, m.w, v.w, a, lr);
 }
 
 // One trip: U float4 groups per stream at i, i+stride, ..., all loads issued before any use.
 // WT > 0: W known at compile time (whole fold unrolled, W*U gradient loads in flight).
 // WT == 0: runtime W, folded four buffers at a time.
 template <int OPT, int WT, int U>
-__device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t stride, uint64_t pol) {
+__device__ __forceinline__ void trip(const DenseParams& a, const float lr, uint64_t i, uint64_t stride, uint64_t pol) {
     float4 acc[U], P[U], M[U], V[U];
     if (WT > 0) {
         float4 G[WT > 0 ? WT : 1][U];
@@ -170,7 +183,7 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        apply4<OPT>(acc[u], P[u], M[u], V[u], a);
+        apply4<OPT>(acc[u], P[u], M[u], V[u], a, lr);
         const uint64_t j = i + u * stride;
         st_f4(reinterpret_cast<float4*>(a.p) + j, P[u]);
         if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + j, M[u]);
@@ -181,13 +194,17 @@ __device__ __forceinline__ void trip(const DenseParams& a, uint64_t i, uint64_t 
 
 template <int OPT, int WT, int U>
 __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
+    if (a.abort_word && *(const volatile uint32_t*)a.abort_word) return;  // never update from gradients that did not all arrive
+    // the step size stays a kernel parameter (constant bank): reading it from device memory into a
+    // register cost 4 % of the C1 step on B200 (0.619 -> 0.648 ms); graph replay re-arms the node instead
+    const float lr = a.lr;
     const uint64_t pol = policy_evict_first();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t i = tid;
-    for (; i + (U - 1) * stride < a.n4; i += U * stride) trip<OPT, WT, U>(a, i, stride, pol);
+    for (; i + (U - 1) * stride < a.n4; i += U * stride) trip<OPT, WT, U>(a, lr, i, stride, pol);
     if (U > 1)
-        for (; i < a.n4; i += stride) trip<OPT, WT, 1>(a, i, stride, pol);
+        for (; i < a.n4; i += stride) trip<OPT, WT, 1>(a, lr, i, stride, pol);
     // scalar tail: n % 4 elements, or the whole slice when a pointer is not 16-byte aligned
     for (uint64_t j = a.n4 * 4 + tid; j < a.n; j += stride) {
         float s = a.g[0][j];
@@ -195,7 +212,7 @@ __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
         float p = OPT == OPT_FOLD ? 0.f : a.p[j], m = 0.f, v = 0.f;
         if (HAS_M(OPT)) m = a.m[j];
         if (HAS_V(OPT)) v = a.v[j];
-        apply1<OPT>(s, p, m, v, a);
+        apply1<OPT>(s, p, m, v, a, lr);
         a.p[j] = p;
         if (HAS_M(OPT)) a.m[j] = m;
         if (HAS_V(OPT)) a.v[j] = v;
@@ -220,13 +237,7 @@ __global__ void fill_uniform_kernel(float* __restrict__ dst, uint64_t n, uint64_
     }
 }
 
-struct Tuning {
-    // measured on B200 (profiles/r1_dense_sweep.md): 256 x 8 x 2 streams Adam W=4 at 6.5 TB/s
-    int threads = 256;
-    int ctas_per_sm = 8;
-    int unroll = 2;
-};
-Tuning g_tuning;
+Tuning g_tuning;  // process-wide default of the stateless entry points; a context carries its own
 
 // largest CTA the kernel's register count allows (1024 threads x > 64 registers does not fit an SM)
 template <typename Kern>
@@ -235,9 +246,20 @@ int max_threads_for(Kern kern) {
     return cudaFuncGetAttributes(&fa, kern) == cudaSuccess ? fa.maxThreadsPerBlock : 256;
 }
 
+// kernel function -> OPT_*, filled as instantiations are first launched: lets a context find the
+// apply nodes of a captured graph (dense_node_opt) and re-arm their step size (dense_node_set_lr)
+std::mutex g_registry_mutex;
+std::map<const void*, int> g_registry;
+
 template <int OPT, int WT, int U>
 cudaError_t launch_k(const DenseParams& a, int grid, int threads, cudaStream_t st) {
     static const int limit = max_threads_for(dense_apply_kernel<OPT, WT, U>);
+    static const bool registered = [] {
+        std::lock_guard<std::mutex> lock(g_registry_mutex);
+        g_registry[(const void*)dense_apply_kernel<OPT, WT, U>] = OPT;
+        return true;
+    }();
+    (void)registered;
     if (threads > limit) {  // keep the thread count of the launch constant: more, smaller CTAs
         const int t2 = limit / 32 * 32;
         grid = (int)(((long long)grid * threads + t2 - 1) / t2);
@@ -267,7 +289,8 @@ cudaError_t launch_w(const DenseParams& a, int grid, int threads, int unroll, cu
     }
 }
 
-int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* const* d_mirrors, void* stream) {
+int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* const* d_mirrors, void* stream,
+                const Tuning& t = g_tuning) {
     B200PS_REQUIRE(a.p && d_grads, B200PS_ERR_INVALID, "null parameter or gradient pointer");
     B200PS_REQUIRE(a.W >= 1 && a.W <= B200PS_MAX_WORKERS, B200PS_ERR_RANGE, "W = %d is outside 1..%d", a.W,
                    B200PS_MAX_WORKERS);
@@ -276,6 +299,7 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     B200PS_REQUIRE(a.n_mirror == 0 || d_mirrors, B200PS_ERR_INVALID, "null mirror list");
     if (opt == OPT_ADAM) B200PS_REQUIRE(a.m && a.v, B200PS_ERR_INVALID, "Adam needs m and v");
     if (opt == OPT_MOMENTUM) B200PS_REQUIRE(a.m, B200PS_ERR_INVALID, "momentum needs the accumulator");
+    if (opt == OPT_FTRL) B200PS_REQUIRE(a.m && a.v, B200PS_ERR_INVALID, "FTRL needs accum and linear");
     if (a.n == 0) return B200PS_OK;
 
     uintptr_t bits = (uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v;
@@ -293,7 +317,6 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
 
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
-    const Tuning t = g_tuning;
     static const int env_load_kind = getenv("B200PS_DENSE_LOAD") ? atoi(getenv("B200PS_DENSE_LOAD")) : 0;  // experiments
     a.load_kind = env_load_kind;
     static const int env_end_fence = getenv("B200PS_DENSE_END_FENCE") ? atoi(getenv("B200PS_DENSE_END_FENCE")) : 0;  // experiments
@@ -306,6 +329,7 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     cudaError_t e = opt == OPT_SGD    ? launch_w<OPT_SGD>(a, grid, t.threads, t.unroll, st)
                     : opt == OPT_ADAM ? launch_w<OPT_ADAM>(a, grid, t.threads, t.unroll, st)
                     : opt == OPT_MOMENTUM ? launch_w<OPT_MOMENTUM>(a, grid, t.threads, t.unroll, st)
+                    : opt == OPT_FTRL ? launch_w<OPT_FTRL>(a, grid, t.threads, t.unroll, st)
                                       : launch_w<OPT_FOLD>(a, grid, t.threads, t.unroll, st);
     B200PS_CUDA(e);
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -313,6 +337,47 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
 }
 
 }  // namespace
+
+int dense_launch(const DenseLaunch& l, const Tuning& t, cudaStream_t stream) {
+    DenseParams a{};
+    a.p = l.p;
+    a.m = l.s1;
+    a.v = l.s2;
+    a.n = l.n;
+    a.W = l.W;
+    a.inv_w = l.inv_w;
+    a.n_mirror = l.n_mirrors;
+    a.lr = l.lr;
+    a.beta1 = l.c1;
+    a.beta2 = l.c2;
+    a.omb1 = l.omb1;
+    a.omb2 = l.omb2;
+    a.eps = l.eps;
+    a.abort_word = l.abort_word;
+    return dense_apply(l.opt, a, l.grads, l.mirrors, (void*)stream, t);
+}
+
+int dense_node_opt(cudaGraphNode_t node) {
+    cudaGraphNodeType ty;
+    if (cudaGraphNodeGetType(node, &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) return -1;
+    cudaKernelNodeParams kp{};
+    if (cudaGraphKernelNodeGetParams(node, &kp) != cudaSuccess) return -1;
+    std::lock_guard<std::mutex> lock(g_registry_mutex);
+    auto it = g_registry.find(kp.func);
+    return it == g_registry.end() ? -1 : it->second;
+}
+
+cudaError_t dense_node_set_lr(cudaGraphExec_t exec, cudaGraphNode_t node, float lr) {
+    cudaKernelNodeParams kp{};
+    cudaError_t e = cudaGraphKernelNodeGetParams(node, &kp);
+    if (e != cudaSuccess) return e;
+    DenseParams a = *static_cast<const DenseParams*>(kp.kernelParams[0]);  // the node's copy of the launch arguments
+    a.lr = lr;
+    void* args[1] = {&a};
+    kp.kernelParams = args;
+    return cudaGraphExecKernelNodeSetParams(exec, node, &kp);
+}
+
 }  // namespace b200ps
 
 using namespace b200ps;
@@ -384,6 +449,24 @@ extern "C" int b200ps_dense_apply_momentum(float* d_params, float* d_accum, cons
     a.lr = lr;
     a.beta1 = momentum;
     return dense_apply(OPT_MOMENTUM, a, d_grads, d_mirrors, stream);
+}
+
+extern "C" int b200ps_dense_apply_ftrl(float* d_params, float* d_accum, float* d_linear, const float* const* d_grads, int W,
+                                       uint64_t n, float inv_w, float lr, float l1, float l2, float* const* d_mirrors,
+                                       int n_mirrors, void* stream) {
+    B200PS_REQUIRE(lr > 0.f && l1 >= 0.f && l2 >= 0.f, B200PS_ERR_RANGE, "FTRL needs lr > 0, l1 >= 0, l2 >= 0");
+    DenseParams a{};
+    a.p = d_params;
+    a.m = d_accum;
+    a.v = d_linear;
+    a.n = n;
+    a.W = W;
+    a.inv_w = inv_w;
+    a.n_mirror = n_mirrors;
+    a.lr = lr;
+    a.beta1 = l1;
+    a.beta2 = 2.0f * l2;
+    return dense_apply(OPT_FTRL, a, d_grads, d_mirrors, stream);
 }
 
 extern "C" int b200ps_fill_uniform(float* d_dst, uint64_t n, uint64_t seed, uint64_t step, uint64_t worker,

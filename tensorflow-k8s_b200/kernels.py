@@ -72,6 +72,18 @@ def dense_apply_momentum(params: torch.Tensor, accum: torch.Tensor, grads: Seque
                                           momentum, mi, len(mirrors), _stream()))
 
 
+def dense_apply_ftrl(params: torch.Tensor, accum: torch.Tensor, linear: torch.Tensor, grads: Sequence[torch.Tensor], lr: float,
+                     l1: float = 0.0, l2: float = 0.0, mirrors: Sequence[torch.Tensor] = (), n: Optional[int] = None,
+                     inv_w: Optional[float] = None) -> None:
+    """TensorFlow's ApplyFtrl with lr_power = -0.5 (accum starts at 0.1, linear at 0)."""
+    n = params.numel() if n is None else n
+    inv_w = inv_w_f32(max(len(grads), 1)) if inv_w is None else inv_w
+    g = _ptr_array([_dev_f32(t, "grad") for t in grads])
+    mi = _ptr_array([_dev_f32(t, "mirror") for t in mirrors])
+    check(lib.b200ps_dense_apply_ftrl(_dev_f32(params, "params"), _dev_f32(accum, "accum"), _dev_f32(linear, "linear"), g,
+                                      len(grads), n, inv_w, lr, l1, l2, mi, len(mirrors), _stream()))
+
+
 def dense_fold(out: torch.Tensor, bufs: Sequence[torch.Tensor], n: Optional[int] = None) -> torch.Tensor:
     """out = ((b0 + b1) + b2) + ... : the per-GPU partial sum of the two-level aggregation."""
     n = out.numel() if n is None else n

@@ -234,8 +234,18 @@ def test_parameter_server_adam_two_shards(oracle):
     for s, x in d.items():
         b, e = x["range"]
         assert same(torch.from_numpy(x["p"]), hp[b:e]) and same(torch.from_numpy(x["m"]), hm[b:e]) and same(torch.from_numpy(x["v"]), hv[b:e])
-    with pytest.raises(ValueError):
-        ps.capture_step()  # Adam: the step size changes every step
+    # Adam replays as a CUDA graph too: the bias-corrected step size is read from device memory
+    for w in range(W):
+        K.fill_uniform(ps.grad_buffer(w), 2, 4, w)
+    g = ps.capture_step()  # step 4 (captured and run)
+    hg = [oracle.fill_uniform(P, 2, 4, w) for w in range(W)]
+    oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 4))
+    g.replay()             # step 5, same gradients
+    oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 5))
+    assert ps.t == 5
+    for s, x in ps.dump().items():
+        b, e = x["range"]
+        assert same(torch.from_numpy(x["p"]), hp[b:e]) and same(torch.from_numpy(x["m"]), hm[b:e]) and same(torch.from_numpy(x["v"]), hv[b:e])
     ps.close()
 
 
@@ -338,4 +348,71 @@ def test_ordered_async_mode(oracle, opt):
             else:
                 oracle.dense_sgd(hp, [hg[w]], 0.05)
     assert ps.t == t and same(ps.replica, hp)
+    ps.close()
+
+
+@pytest.mark.parametrize("W,n", [(1, 5), (4, 4099), (5, 300_001)])
+def test_ftrl_bit_exact(oracle, W, n):
+    p = oracle.fill_uniform(n, 1, 0, 0)
+    acc, lin = np.full(n, 0.1, np.float32), np.zeros(n, np.float32)
+    dp, da, dl = dev(p), dev(acc), dev(lin)
+    dg = [torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(W)]
+    for t in (1, 2, 3, 4):
+        grads = [oracle.fill_uniform(n, 2, t, w, threads=4) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(dg[w], 2, t, w)
+        K.dense_apply_ftrl(dp, da, dl, dg, 0.05, 0.001, 0.01)
+        oracle.dense_ftrl(p, acc, lin, grads, 0.05, 0.001, 0.01, threads=4)
+    assert same(dp, p) and same(da, acc) and same(dl, lin)
+    assert n < 1000 or ((p == 0).any() and (p != 0).any())  # both branches of the l1 clip were taken
+
+
+def test_parameter_server_ftrl_with_checkpoint(oracle, tmp_path):
+    sizes, S, W = [50_000, 3, 7_000], 2, 3
+    kw = dict(optimizer="ftrl", lr=0.05, l1=0.001, l2=0.01)
+    ps = b200ps.ParameterServer(sizes, S, W, **kw)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp, ha, hl = oracle.fill_uniform(P, 1, 0, 0), np.full(P, 0.1, np.float32), np.zeros(P, np.float32)
+    for t in (1, 2, 3):
+        hg = [oracle.fill_uniform(P, 2, t, w) for w in range(W)]
+        for w in range(W):
+            K.fill_uniform(ps.grad_buffer(w), 2, t, w)
+        ps.step()
+        oracle.dense_ftrl(hp, ha, hl, hg, 0.05, 0.001, 0.01)
+        if t == 2:
+            ps.save(str(tmp_path))
+    for s, x in ps.dump().items():
+        b, e = x["range"]
+        assert same(torch.from_numpy(x["p"]), hp[b:e]) and same(torch.from_numpy(x["m"]), ha[b:e]) and same(torch.from_numpy(x["v"]), hl[b:e])
+    q = b200ps.ParameterServer(sizes, S, W, **kw)
+    q.load(str(tmp_path))
+    for w in range(W):
+        K.fill_uniform(q.grad_buffer(w), 2, 3, w)
+    q.step()
+    assert torch.equal(q.replica, ps.replica)
+    ps.close()
+    q.close()
+
+
+def test_step_host_adam_matches_oracle_and_per_context_tuning(oracle):
+    """The pipelined host step (several chunks per slice) with Adam, on a context with its own
+    launch geometry: bit-exact; the process-wide tuning of the stateless entry points is untouched."""
+    sizes, S, W = [300_000, 77, 50_000], 2, 4
+    ps = b200ps.ParameterServer(sizes, S, W, optimizer="adam", lr=1e-3, chunk_elems=65_536, tuning=(128, 4, 1))
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp, hm, hv = oracle.fill_uniform(P, 1, 0, 0), np.zeros(P, np.float32), np.zeros(P, np.float32)
+    out = torch.empty(P, dtype=torch.float32).pin_memory()
+    for t in (1, 2, 3):
+        hg = [oracle.fill_uniform(P, 2, t, w) for w in range(W)]
+        host_g = {w: torch.from_numpy(hg[w]).pin_memory() for w in range(W)}
+        ps.step_host(host_g, {0: out})
+        ps.host_sync()
+        oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t))
+        assert np.array_equal(out.numpy().view(np.uint32), hp.view(np.uint32)), f"step {t}"
+    ps.step()  # a device step right after a host step is ordered behind its copy-out
+    oracle.dense_adam(hp, hm, hv, hg, oracle.adam_scalars(1e-3, 0.9, 0.999, 1e-8, 4))
+    torch.cuda.synchronize()
+    assert same(ps.replica, hp) and ps.t == 4
     ps.close()

@@ -51,3 +51,29 @@ def test_restart_policies(tmp_path):
     assert launcher.launch(c, 2, [sys.executable, "-c", prog], restart_policy="OnFailure") == 0
     os.remove(marker)
     assert launcher.launch(c, 2, [sys.executable, "-c", prog], restart_policy="Never") == 3
+
+
+def test_onfailure_gives_up_after_max_restarts_and_returns_the_failing_code(tmp_path):
+    """Rank 0 always fails: the gang is restarted max_restarts times (never a lone rank, never after
+    the job has failed for good) and the launcher returns rank 0's code, not a stopped peer's -15."""
+    c = b200ps.Cluster.from_tfjob(C1)
+    log = tmp_path / "starts"
+    prog = (f"import os, sys, time; open({str(log)!r}, 'a').write(os.environ['RANK'] + ':' + os.environ['B200PS_RESTART_COUNT'] + ' ')\n"
+            "if os.environ['RANK'] == '0': sys.exit(7)\n"
+            "time.sleep(30)\n")
+    assert launcher.launch(c, 2, [sys.executable, "-c", prog], restart_policy="OnFailure", max_restarts=2) == 7
+    starts = sorted(log.read_text().split())
+    assert starts == ["0:0", "0:1", "0:2", "1:0", "1:1", "1:2"]  # three gang starts, each with its restart count
+
+
+def test_chief_decides_completion_and_cleanup_hook_runs(tmp_path):
+    c = b200ps.Cluster.from_tfjob(C1)
+    done = tmp_path / "cleaned"
+    # rank 1 (a pure PS / worker rank) never exits on its own; the chief's rank finishes
+    prog = "import os, time\nif os.environ['RANK'] != '0': time.sleep(60)\n"
+    hook = [sys.executable, "-c", f"import os; open({str(done)!r}, 'w').write(os.environ['B200PS_JOB_STATUS'])"]
+    assert launcher.launch(c, 2, [sys.executable, "-c", prog], completion="chief", cleanup=hook, chief_grace=0.5) == 0
+    assert done.read_text() == "succeeded"
+    bad = "import sys; sys.exit(4)"
+    assert launcher.launch(c, 2, [sys.executable, "-c", bad], cleanup=hook) == 4
+    assert done.read_text() == "failed"

@@ -212,3 +212,23 @@ def test_chunked_fold_of_a_130k_entry_hot_row_against_the_plain_left_fold(oracle
     c = oracle.sparse_apply_sgd(t0.copy(), 0, g[:k].copy(), np.zeros(k, np.int64), inv_w, lr)[0]
     q = t0[0] - lr * (np.cumsum(g[:k], axis=0, dtype=np.float32)[-1] * inv_w)
     assert np.array_equal(c.view(np.uint32), q.view(np.uint32))
+
+
+def test_ftrl_kat_and_c_vs_numpy(oracle, nporacle):
+    """TF ApplyFtrl, lr_power = -0.5.  p = 0, accum = 0.1, linear = 0, g = 1, lr = 1, l1 = l2 = 0:
+    na = 1.1, linear = 1, p = -1 / sqrt(1.1).  With l1 >= |linear| the weight is clipped to exactly 0."""
+    p, a, l = np.zeros(1, np.float32), np.full(1, 0.1, np.float32), np.zeros(1, np.float32)
+    oracle.dense_ftrl(p, a, l, [np.ones(1, np.float32)], 1.0, 0.0, 0.0)
+    assert p[0] == np.float32(-1.0) / np.sqrt(np.float32(1.1)) and a[0] == np.float32(1.1) and l[0] == 1.0
+    p, a, l = np.zeros(1, np.float32), np.full(1, 0.1, np.float32), np.zeros(1, np.float32)
+    oracle.dense_ftrl(p, a, l, [np.ones(1, np.float32)], 1.0, 2.0, 0.0)  # l1 = 2 > |linear| = 1
+    assert p[0] == 0.0 and l[0] == 1.0
+    n, W = 5003, 3
+    p, a, l = oracle.fill_uniform(n, 1, 0, 0), np.full(n, 0.1, np.float32), np.zeros(n, np.float32)
+    q, b, m = p.copy(), a.copy(), l.copy()
+    for t in (1, 2, 3, 4):
+        gs = [oracle.fill_uniform(n, 2, t, w) for w in range(W)]
+        oracle.dense_ftrl(p, a, l, gs, 0.05, 0.001, 0.01, threads=3)
+        q, b, m = nporacle.dense_ftrl(q, b, m, gs, 0.05, 0.001, 0.01)
+    assert np.array_equal(p, q) and np.array_equal(a, b) and np.array_equal(l, m)
+    assert (p == 0).any() and (p != 0).any()  # both branches of the l1 clip were taken

@@ -23,8 +23,8 @@ def main():
     ps = b200ps.ParameterServer([n], world, world, optimizer="sgd", rank=rank, world=world)
     P = ps.plan.P
     st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    me = ps.arena.ptr
-    peers = [ps.peer_base[r] for r in range(world) if r != rank]
+    me = ps.arena_base(rank)
+    peers = [ps.arena_base(r) for r in range(world) if r != rank]
     out = torch.empty(P, dtype=torch.float32, device="cuda")
     pa = lambda v: (C.c_void_p * max(len(v), 1))(*v)
 
