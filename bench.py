@@ -40,8 +40,8 @@ def parse():
     ap.add_argument("--ids", default="zipf", choices=["zipf", "uniform"], help="id distribution of --workload c2")
     ap.add_argument("--rows", type=int, default=10_000_000, help="table rows of --workload c2")
     ap.add_argument("--transport", default="peer", choices=["peer", "nccl"])
-    ap.add_argument("--barrier", default="nccl", choices=["peer", "nccl"],
-                    help="cross-rank barrier of a step when N > 1: a 4-byte NCCL all-reduce, or flags in peer memory")
+    ap.add_argument("--barrier", default="peer", choices=["peer", "nccl"],
+                    help="--workload c2 only: cross-rank barrier of the sparse step when N > 1")
     ap.add_argument("--overlap", action="store_true",
                     help="N > 1: pipeline the local folds with the NVLink exchange over two streams (helps at N=2, not at N=8)")
     ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
@@ -51,14 +51,25 @@ def parse():
     ap.add_argument("--no-profile", action="store_true", help="N > 1: do not bracket the phases of a step with events")
     ap.add_argument("--no-graph", action="store_true", help="SGD workloads on one GPU: launch every step instead of replaying a CUDA graph")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="skip the brief C3 / C0 / C2 measurements that ride along")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps, capped at 30")
     return ap.parse_args()
 
 
+def _synth():
+    """tensorflow-k8s_b200/synth.py loaded by path: pure-Python shape lists and the id generator, WITHOUT
+    importing the package (which would dlopen libb200ps.so) -- the reference arm stays oracle-only."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("_b200ps_synth", os.path.join(ROOT, "tensorflow-k8s_b200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def workload(name: str, n_gpus: int):
     """(label, variable sizes, S, W, optimizer) -- per-GPU density held fixed as N grows."""
-    from b200ps import synth
-
+    synth = _synth()
     if name == "c1":
         return ("C1 dense MLP 1024-8192-8192-2048-4096, 100685824 fp32 params, Adam, "
                 f"{2 * n_gpus} PS shards + {4 * n_gpus} workers", synth.mlp_c1_variables(), 2 * n_gpus, 4 * n_gpus, "adam")
@@ -67,6 +78,22 @@ def workload(name: str, n_gpus: int):
                 synth.resnet50_c3_variables(), n_gpus, n_gpus, "adam")
     return (f"C0 linear regression 1M params, SGD, {n_gpus} PS + {2 * n_gpus} workers", synth.linreg_c0_variables(),
             n_gpus, 2 * n_gpus, "sgd")
+
+
+def tfjob_spec(name: str, S: int, W: int) -> dict:
+    """The TFJob the bench drives (v1alpha1 list form): S PS replicas + W WORKER replicas."""
+    return {"apiVersion": "tensorflow.org/v1alpha1", "kind": "TFJob", "metadata": {"name": f"bench-{name}"},
+            "spec": {"replicaSpecs": [{"replicas": S, "tfReplicaType": "PS"}, {"replicas": W, "tfReplicaType": "WORKER"}]}}
+
+
+def dense_config(label, sizes, S, W, opt):
+    """`config` of the JSON line -- identical in both arms (it names the workload, not the implementation)."""
+    P = sum((n + 1023) // 1024 * 1024 for n in sizes)
+    step_bytes = (4 * W + (24 if opt == "adam" else 8)) * P
+    return {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": P,
+            "l2": (f"inputs exceed L2 (a step streams {step_bytes / 1e9:.2f} GB >> 126 MB), no flush needed") if step_bytes > (512 << 20)
+            else (f"working set ({step_bytes / 1e6:.0f} MB per step) fits the 126 MB L2 and is NOT flushed between steps: "
+                  "an L2-resident, launch-bound figure, not an HBM one")}
 
 
 def hbm_peak():
@@ -184,12 +211,13 @@ def reference_arm(args):
     if rank != 0:
         return
     label, sizes, S, W, opt = workload(args.workload, args.gpus)
-    val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, args.steps, min(args.warmup, 3))
+    warm = max(args.warmup, 3)
+    val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, args.steps, warm)
     print(json.dumps({
         "impl": "reference", "metric": "ps_steps_per_sec", "value": round(val, 3), "unit": "worker-steps/s",
-        "n_gpus": args.gpus, "steps": done, "warmup": min(args.warmup, 3), "ms_per_step": round(ms, 3),
+        "n_gpus": args.gpus, "steps": done, "warmup": warm, "ms_per_step": round(ms, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt},
+        "config": dense_config(label, sizes, S, W, opt),
         "ps_steps_per_sec": round(val / W, 3), "algorithmic_GBps": round(gbs, 1),
         "cpu_baseline": {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
                          "sample": f"{done} full steps of the workload (every slice, every worker); substitute CPU "
@@ -213,9 +241,9 @@ def sparse_cpu(rows, ids_kind, steps, seconds):
     all host threads (OpenMP over ids / unique rows); the stable sort is a serial qsort."""
     import numpy as np
 
-    from b200ps import synth
     from oracle import c_oracle as O
 
+    synth = _synth()
     dim, W, B = C2["dim"], C2["W"], C2["B"]
     nt = O.use_all_cores()
     table = O.fill_uniform(rows * dim, 1, 0, 0, threads=nt).reshape(rows, dim)
@@ -239,6 +267,22 @@ def sparse_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     rows, dim, S, W, B = args.rows, C2["dim"], C2["S"], C2["W"], C2["B"]
     label = f"C2 Wide&Deep embedding {rows}x{dim}, {S} PS shards, {W} workers, {B} ids/worker/step, {args.ids} ids, SGD"
+    if args.impl != "reference":
+        import torch
+        import torch.distributed as dist
+
+        world, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        out = sparse_measure(args, args.ids, args.steps, max(args.warmup, 3), e2e=not args.no_e2e, cpu=not args.no_cpu,
+                             graph=not args.no_graph)
+        if rank == 0:
+            print(json.dumps(out))
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     if args.impl == "reference":
         if rank == 0:
             val, done, ms = sparse_cpu(rows, args.ids, args.steps, 120.0)
@@ -252,19 +296,23 @@ def sparse_arm(args):
                               "e2e": {"value": round(val, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 0,
                                       "d2h_bytes_per_step": 0}}))
         return
+
+
+def sparse_measure(args, ids_kind, steps, warmup, e2e=False, cpu=False, graph=True):
+    """One C2 measurement on the current process group (every rank calls it); returns the JSON object."""
     import torch
     import torch.distributed as dist
 
     import b200ps
     from b200ps import kernels as K, synth
 
-    world, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = torch.cuda.current_device()
+    rows, dim, S, W, B = args.rows, C2["dim"], C2["S"], C2["W"], C2["B"]
+    label = f"C2 Wide&Deep embedding {rows}x{dim}, {S} PS shards, {W} workers, {B} ids/worker/step, {ids_kind} ids, SGD"
     tab = b200ps.EmbeddingTable(rows, dim, S, W, B, optimizer="sgd", lr=C2["lr"], rank=rank, world=world, barrier=args.barrier)
     tab.init_uniform(1)
-    ids = synth.make_ids(args.ids, rows, W, B, 1)
+    ids = synth.make_ids(ids_kind, rows, W, B, 1)
     outs = {}
     for w in tab.local_workers:
         tab.ids[w].copy_(torch.from_numpy(ids[w]))
@@ -295,36 +343,36 @@ def sparse_arm(args):
             ev[3].record()
         tab._barrier()
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         step()
     sync()
     plan = tab.plan()
     graph_ms = None
-    if world == 1 and not args.no_graph:  # the same step replayed as one CUDA graph (no per-launch host work)
+    if world == 1 and graph:  # the same step replayed as one CUDA graph (no per-launch host work)
         gr = tab.capture_step()
         for _ in range(3):
             gr.replay()
         sync()
         ga, gb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ga.record()
-        for _ in range(args.steps):
+        for _ in range(steps):
             gr.replay()
         gb.record()
         sync()
-        graph_ms = ga.elapsed_time(gb) / args.steps
+        graph_ms = ga.elapsed_time(gb) / steps
     sampler = ClockSampler(local)
     sampler.start()
     l0 = K.launch_count()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for i in range(args.steps):
+    for i in range(steps):
         step(evs[i])
     b.record()
     sync()
     clocks = sampler.finish()
     launches = K.launch_count() - l0
-    ms = a.elapsed_time(b) / args.steps
+    ms = a.elapsed_time(b) / steps
     launched_ms = ms
     if graph_ms is not None and graph_ms < ms:
         ms = graph_ms  # headline = the graph replay; the per-phase breakdown below is from the launched run
@@ -332,15 +380,15 @@ def sparse_arm(args):
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    g_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
-    s_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
-    p_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
+    g_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / steps
+    s_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / steps
+    p_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / steps
     d4 = 4 * dim
     gather_bytes = W * B * 8 + (plan["n_kept"] + len(tab.local_workers) * B) * d4  # ids scanned, rows served (read) + landed (write)
     apply_bytes = plan["n_kept"] * (4 + d4) + plan["n_unique"] * (2 * d4 + 4)  # perm + rows; unique id + row R/W
     peak, peak_src = hbm_peak()
-    e2e = None
-    if not args.no_e2e:
+    e2e_d = None
+    if e2e:
         # host buffers: ids + gradient rows of every local worker go H2D, the pulled rows come back D2H
         h_ids = {w: torch.from_numpy(ids[w]).pin_memory() for w in tab.local_workers}
         h_gr = {w: torch.empty(B, dim, dtype=torch.float32).pin_memory() for w in tab.local_workers}
@@ -360,32 +408,33 @@ def sparse_arm(args):
         for _ in range(3):
             host_step()
         sync()
-        n_e = min(args.steps, 30)
+        n_e = min(steps, 30)
         a.record()
         for _ in range(n_e):
             host_step()
         b.record()
         sync()
         e_ms = a.elapsed_time(b) / n_e
-        e2e = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": W * B * (8 + d4),
+        e2e_d = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": W * B * (8 + d4),
                "d2h_bytes_per_step": W * B * d4, "ms_per_step": round(e_ms, 3), "steps": n_e,
                "api": "b200ps.EmbeddingTable: ids + gradient rows H2D, pull -> D2H, push_step"}
-    cpu = None
-    if world == 1 and not args.no_cpu:
-        tab.close()
-        torch.cuda.empty_cache()
-        val, done, cms = sparse_cpu(rows, args.ids, 10 ** 6, args.cpu_seconds)
-        cpu = {"value": round(val, 3), "unit": "worker-steps/s", "cores": ncores(), "kind": "port",
+    longest = int(plan["seg_offset"][1:].astype("int64").__sub__(plan["seg_offset"][:-1]).max())
+    tab.close()
+    del tab, outs
+    torch.cuda.empty_cache()
+    cpu_d = None
+    if world == 1 and cpu:
+        val, done, cms = sparse_cpu(rows, ids_kind, 10 ** 6, args.cpu_seconds if cpu is True else cpu)
+        cpu_d = {"value": round(val, 3), "unit": "worker-steps/s", "cores": ncores(), "kind": "port",
                "sample": f"{done} full steps ({cms:.0f} ms each); substitute CPU reference (oracle/ps_oracle.c: OpenMP "
                          "gather/apply, serial sort)"}
-    if rank == 0:
-        print(json.dumps({
+    return {
             "metric": "ps_steps_per_sec", "value": round(W * 1e3 / ms, 3), "unit": "worker-steps/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True,
+            "steps": steps, "warmup": warmup, "ms_per_step": round(ms, 4), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
             "config": {"workload": label, "cuda_graph": graph_ms is not None and graph_ms <= launched_ms,
                        "ms_per_step_launched": round(launched_ms, 4), "n_kept": int(plan["n_kept"]), "n_unique": int(plan["n_unique"]),
-                       "longest_segment": int(plan["seg_offset"][1:].astype("int64").__sub__(plan["seg_offset"][:-1]).max()),
+                       "longest_segment": longest,
                        "l2": "table 2.56 GB and 0.54 GB of gradient rows per step exceed L2; no flush"},
             "ps_steps_per_sec": round(1e3 / ms, 3),
             "phases_ms": {"serve_pull": round(g_ms, 4), "route+barrier+sort_segment": round(s_ms, 4), "apply": round(p_ms, 4)},
@@ -397,38 +446,98 @@ def sparse_arm(args):
                                "frac": round(apply_bytes / p_ms / 1e6 / peak, 4), "traffic": ncu_traffic("sparse_apply_kernel<16,sgd>"),
                                "kernel": "sparse_apply_kernel<16,sgd>",
                                "algorithmic_bytes_per_step": int(apply_bytes)},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+            "cpu_baseline": cpu_d, "e2e": e2e_d, "gpu_launches": int(launches), "clocks": clocks}
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def main():
-    args = parse()
-    if args.workload == "c2":
-        return sparse_arm(args)
-    if args.impl == "reference":
-        return reference_arm(args)
+NVLINK_PEAK_GBS = 770.0  # measured peer copy per direction per GPU on this pool (B200_PROFILING.md); 900 nominal
 
+
+def make_ps(name, args, rank, world, graph=False, scale=1, aggregate=None):
+    """The TF_CONFIG-driven path: TFJob spec -> launcher placement -> this rank's TF_CONFIG / B200PS_TASKS ->
+    b200ps.rank.job_from_env -> ParameterServer.  `scale` > 1 shrinks every variable (parity pre-check)."""
+    import b200ps
+    from b200ps import launcher, rank as rankmod
+
+    label, sizes, S, W, opt = workload(name, world)
+    if scale > 1:
+        sizes = [max(1, n // scale) for n in sizes]
+    cluster = b200ps.Cluster.from_tfjob(tfjob_spec(name, S, W))
+    env = launcher.rank_env(launcher.plan_tasks(cluster, world), rank, world, int(os.environ.get("MASTER_PORT", "29500")))
+    job = rankmod.job_from_env({**env, "RANK": str(rank), "WORLD_SIZE": str(world)})
+    assert (job.shards, job.workers) == (S, W)
+    ps = b200ps.ParameterServer(sizes, job.shards, job.workers, optimizer=opt, lr=1e-3 if opt == "adam" else 0.01, rank=rank,
+                                world=world, transport=args.transport, aggregate=aggregate or args.aggregate, overlap=args.overlap,
+                                use_graph=graph, cluster=job.cluster)
+    return ps, label, sizes, S, W, opt
+
+
+def parity_check(name, args, rank, world, steps=2, scale=64):
+    """Two steps of the SAME plan (same S, W, aggregation, transport, barriers, graph replay) on variables
+    shrunk by `scale`, every rank's replica and optimizer state compared bit for bit with the oracle
+    (the checker); the verdict is all-reduced.  Exits non-zero on a mismatch."""
+    import numpy as np
     import torch
     import torch.distributed as dist
 
-    import b200ps
+    from b200ps import kernels as K
+    from oracle import c_oracle as O
+
+    ps, label, sizes, S, W, opt = make_ps(name, args, rank, world, graph=not args.no_graph, scale=scale)
+    ps.init_uniform(1)
+    P = ps.plan.P
+    hp, hm, hv = O.fill_uniform(P, 1, 0, 0, threads=4), np.zeros(P, np.float32), np.zeros(P, np.float32)
+    inv_w = np.float32(1.0) / np.float32(W)
+    for t in range(1, steps + 1):
+        for w in ps.plan.local_workers:
+            K.fill_uniform(ps.grad_buffer(w), 2, t, w)
+        ps.step()
+        hg = [O.fill_uniform(P, 2, t, w, threads=4) for w in range(W)]
+        if ps.plan.two_level:
+            hg = O.two_level_partials(hg, world, threads=4)
+        if opt == "adam":
+            O.dense_adam(hp, hm, hv, hg, O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, t), threads=4, inv_w=inv_w)
+        else:
+            O.dense_sgd(hp, hg, 0.01, threads=4, inv_w=inv_w)
+    exact = args.transport == "peer" and args.aggregate != "multimem"
+    d = ps.dump()
+    got = ps.replica.cpu().numpy()
+    if exact:
+        ok = np.array_equal(got.view(np.uint32), hp.view(np.uint32))
+        for sh, x in d.items():
+            b, e = x["range"]
+            if "m" in x:
+                ok = ok and np.array_equal(x["m"].view(np.uint32), hm[b:e].view(np.uint32))
+                ok = ok and np.array_equal(x["v"].view(np.uint32), hv[b:e].view(np.uint32))
+    else:  # library / in-switch summation order: the north-star tolerance
+        ok = bool(np.allclose(got, hp, rtol=1e-6, atol=1e-7))
+    ps.close()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = bool(flag.item())
+    res = {"n": world, "ok": ok, "elements": int(P), "steps": steps, "shards": S, "workers": W,
+           "compared": "every rank's replica + optimizer state vs oracle, " + ("bit-exact" if exact else "rtol 1e-6"),
+           "same_plan_as_timed_run": True, "variables_scaled_by": f"1/{scale}"}
+    if not ok:
+        if rank == 0:
+            print(json.dumps({"parity_checked": res}), flush=True)
+        raise SystemExit(3)
+    return res
+
+
+def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=False, graph=None, profile=True):
+    """Device-resident step timing (+ optional host-buffer e2e and CPU baseline) of one dense workload."""
+    import torch
+    import torch.distributed as dist
+
     from b200ps import kernels as K
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    label, sizes, S, W, opt = workload(args.workload, world)
-    ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, rank=rank, world=world, transport=args.transport,
-                                aggregate=args.aggregate, overlap=args.overlap)
+    label, sizes, S, W, opt = workload(name, world)
+    cfg = dense_config(label, sizes, S, W, opt)
+    small = cfg["params_padded"] * (4 * W + 24) < (512 << 20)
+    graphed = (small if graph is None else graph) and not args.no_graph  # launch-bound workloads replay one CUDA graph per step
+    ps, *_ = make_ps(name, args, rank, world, graph=graphed)
     ps.init_uniform(1)
     for w in ps.plan.local_workers:
         K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
@@ -446,145 +555,169 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- device-resident timing: `value` and the roofline ----
-    do_step = ps.step
-    graphed = world == 1 and opt == "sgd" and not args.no_graph
-    if graphed:  # launch-bound workload (C0): replay the step's launches as one CUDA graph
-        do_step = ps.capture_step().replay
-    for _ in range(max(args.warmup, 3)):
-        do_step()
+    stream = torch.cuda.Stream()  # a real stream: the step is ordered on it (the legacy default stream serialises)
     sync()
-    sampler = ClockSampler(local)
-    sampler.start()
-    launches0 = K.launch_count()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    ps.profile = world > 1 and not ps.overlap and not args.no_profile
-    host_t0 = time.perf_counter()
-    ev[0].record()
-    for i in range(args.steps):
-        if world == 1:
-            kev[i][0].record()
-            do_step()
-            kev[i][1].record()
-        else:
-            do_step()
-    ev[1].record()
-    host_ms = 1e3 * (time.perf_counter() - host_t0) / args.steps  # time the host needed to ENQUEUE a step
-    sync()
-    phases = ps.phase_ms() if ps.profile else None
-    ps.profile = False
-    per_rank = None
-    if world > 1 and phases is not None:  # every rank's own kernel times: the step waits for the slowest
-        per_rank = [None] * world
-        dist.all_gather_object(per_rank, {k: round(v, 4) for k, v in phases.items()})
-    clocks = sampler.finish()
-    launches = K.launch_count() - launches0
-    ms_total = reduce_max(ev[0].elapsed_time(ev[1]))
-    ms_step = ms_total / args.steps
-    steps_per_s = 1e3 / ms_step
-    n_kernels_step = len([L for L in ps.plan.launches if L.end > L.begin])
-    bytes_launch = ps.algorithmic_bytes_per_step() / max(n_kernels_step, 1)
-    if world == 1:
-        k_ms = sum(a.elapsed_time(b) for a, b in kev) / (args.steps * max(n_kernels_step, 1))
-    else:
-        k_ms = None
+    with torch.cuda.stream(stream):
+        for _ in range(warmup):
+            ps.step()
+        sync()
+        sampler = ClockSampler(local)
+        sampler.start()
+        launches0 = K.launch_count()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        host_t0 = time.perf_counter()
+        ev[0].record()
+        for i in range(steps):
+            ps.step()
+        ev[1].record()
+        host_ms = 1e3 * (time.perf_counter() - host_t0) / steps  # time the host needed to ENQUEUE a step
+        sync()
+        clocks = sampler.finish()
+        launches = K.launch_count() - launches0
+        ms_step = reduce_max(ev[0].elapsed_time(ev[1])) / steps
+        # phases: a second, shorter pass with events around fold / apply / barriers (adds ~10 % at N = 8,
+        # so it is not the timed run)
+        phases, per_rank = None, None
+        if profile and not args.no_profile:
+            ps.profile = True
+            for _ in range(min(steps, 20)):
+                ps.step()
+            sync()
+            phases = {k: round(v, 4) for k, v in ps.phase_ms().items()}
+            ps.profile = False
+            if world > 1:
+                per_rank = [None] * world
+                dist.all_gather_object(per_rank, phases)
+    n_launch = len([L for L in ps.plan.launches if L.end > L.begin])
+    step_bytes = ps.algorithmic_bytes_per_step()
     peak, peak_src = hbm_peak()
-    roofline = None
-    kname = f"dense_apply_kernel<{opt},W={W}>"
-    if k_ms:
-        ach = bytes_launch / k_ms / 1e6
+    kname = f"dense_apply_kernel<{opt},W={len(ps.plan.launches[0].grad_src) if ps.plan.launches else W}>"
+    if world == 1:
+        # one GPU: the step IS its apply launches (back to back on one stream), so the average launch
+        # duration is step time / launches; phases["apply"] (events around the launches) agrees
+        k_ms = (phases["apply"] if phases else ms_step) / max(n_launch, 1)
+        ach = step_bytes / max(n_launch, 1) / k_ms / 1e6
         roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                    "traffic": ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
-                    "launches_per_step": n_kernels_step}
-    elif phases and n_kernels_step:
-        # N > 1: the apply kernels read G-1 of their G partial sums (or W - W/G gradients) over NVLink,
-        # so HBM is not their bound; the figure is reported against it for continuity only
-        k_ms = phases["apply"] / n_kernels_step
-        ach = bytes_launch / k_ms / 1e6
-        roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                    "traffic": None, "kernel": kname + " (peer loads/stores: NVLink-bound at N>1)", "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": int(bytes_launch), "avg_launch_ms": round(k_ms, 5),
-                    "launches_per_step": n_kernels_step, "phases_ms": {k: round(v, 4) for k, v in phases.items()},
-                    "phases_ms_per_rank": per_rank}
-
-    if roofline is None and world > 1:
-        # pipelined multi-GPU step: the exchange is the bound.  Per step a GPU receives the partial
-        # sums (or gradients) of its slices from the other GPUs plus every other owner's updated
-        # slices into its replica, all on the inbound direction of its NVLink ports.
+                    "traffic": ncu_traffic(f"dense_apply_kernel<{opt},W={W}>"), "kernel": kname, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": int(step_bytes / max(n_launch, 1)), "avg_launch_ms": round(k_ms, 5),
+                    "launches_per_step": n_launch}
+    else:
+        # N > 1: per step a GPU receives the partial sums (or gradients) of its slices from the other GPUs
+        # plus every other owner's updated slices into its replica -- all inbound on its NVLink ports
         mine = sum(L.end - L.begin for L in ps.plan.launches)
         inbound = 4 * (sum((L.end - L.begin) * sum(1 for r, _ in L.grad_src if r != rank) for L in ps.plan.launches)
                        + (ps.plan.P - mine))
         inbound = reduce_max(float(inbound))
         ach = inbound / ms_step / 1e6
-        roofline = {"bound": "nvlink", "achieved": round(ach, 1), "peak": 770.0, "unit": "GB/s", "frac": round(ach / 770.0, 4),
-                    "traffic": None, "kernel": kname + " + dense_fold, pipelined over two streams",
+        roofline = {"bound": "nvlink", "achieved": round(ach, 1), "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
+                    "frac": round(ach / NVLINK_PEAK_GBS, 4), "traffic": None,
+                    "kernel": kname + " (peer loads = push, peer stores = pull) + dense_fold + 2 peer barriers",
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); 900 nominal",
                     "inbound_bytes_per_gpu_per_step": int(inbound),
-                    "note": "N > 1: peer loads (push) and peer stores (pull) share each link direction, so the step is "
-                            "NVLink-bound; achieved = inbound bytes / whole step time (folds and barrier included)"}
+                    "note": "achieved = inbound NVLink bytes of the busiest GPU / whole step time (local fold and barriers included)"}
+    out = {"metric": "ps_steps_per_sec", "value": round(W * 1e3 / ms_step, 3), "unit": "worker-steps/s", "n_gpus": world,
+           "steps": steps, "warmup": warmup, "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+           "impl_config": {"transport": args.transport if world > 1 else "local",
+                           "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
+                           "barrier": "peer-memory flags (device-side epoch)" if world > 1 else "none",
+                           "pipelined": bool(ps.overlap), "cuda_graph": bool(graphed),
+                           "driven_by": "TFJob spec -> launcher placement -> TF_CONFIG / B200PS_TASKS -> b200ps.rank.job_from_env"},
+           "ps_steps_per_sec": round(1e3 / ms_step, 3), "host_enqueue_ms_per_step": round(host_ms, 4),
+           "algorithmic_GBps_per_gpu": round(step_bytes / ms_step / 1e6, 1), "roofline": roofline,
+           "phases_ms": phases, "phases_ms_per_rank": per_rank, "gpu_launches": int(launches), "clocks": clocks}
 
     # ---- end to end with HOST buffers ----
-    e2e = None
-    if not args.no_e2e:
+    if e2e:
         P = ps.plan.P
         hg = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
-        # pull: one pinned host replica per GPU, shared by the workers placed on it (exactly as they
-        # share the device replica)
+        # pull: one pinned host replica per GPU, shared by the workers placed on it (as they share the device replica)
         ho = {ps.plan.local_workers[0]: torch.empty(P, dtype=torch.float32).pin_memory()} if ps.plan.local_workers else {}
         for w in hg:
             hg[w].copy_(ps.grad_buffer(w))
         sync()
-        n_e2e = args.e2e_steps or min(args.steps, 30)
-        for _ in range(3):
-            ps.step_host(hg, ho)
-        sync()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(n_e2e):
-            ps.step_host(hg, ho)
-        b.record()
-        sync()
+        n_e2e = args.e2e_steps or min(steps, 30)
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                ps.step_host(hg, ho)
+            sync()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(n_e2e):
+                ps.step_host(hg, ho)
+            b.record()
+            ps.host_sync()
+            sync()
         e_ms = reduce_max(a.elapsed_time(b)) / n_e2e
-        # whole-job bytes (every rank moves its own workers' buffers)
-        e2e = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
-               "d2h_bytes_per_step": 4 * P * world, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
-               "ps_steps_per_sec": round(1e3 / e_ms, 3),
-               "pcie_bound_ms": round(4 * P * len(ps.plan.local_workers) / 55e6, 2),
-               "api": "b200ps.ParameterServer.step_host (every worker's pinned host gradient in, pulled parameters out "
-                      "to one pinned host replica per GPU)"}
+        out["e2e"] = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
+                      "d2h_bytes_per_step": 4 * P * world, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
+                      "ps_steps_per_sec": round(1e3 / e_ms, 3),
+                      "pcie_bound_ms": round(4 * P * len(ps.plan.local_workers) / 55e6, 2),
+                      "api": "b200ps_dense_step_host via b200ps.ParameterServer.step_host (every worker's pinned host gradient in, "
+                             "pulled parameters out to one pinned host replica per GPU; chunk-pipelined inside the library)"}
         del hg, ho
-
+    ps.close()
+    del ps
+    torch.cuda.empty_cache()
     # ---- CPU baseline (rank 0, N = 1 only) ----
-    cpu = None
-    if world == 1 and not args.no_cpu:
-        ps.close()
-        torch.cuda.empty_cache()
-        val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=args.cpu_seconds)
-        cpu = {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
-               "sample": f"{done} full steps ({ms:.1f} ms each, {gbs:.0f} GB/s algorithmic) of the same workload within "
-                         f"{args.cpu_seconds:.0f} s; substitute CPU reference (oracle/ps_oracle.c, OpenMP)"}
-        v1, d1, ms1, _, g1 = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=args.cpu_seconds / 4, threads=1)
-        cpu["single_thread"] = {"value": round(v1, 3), "ms_per_step": round(ms1, 1), "algorithmic_GBps": round(g1, 1), "steps": d1}
+    if world == 1 and cpu:
+        secs = args.cpu_seconds if cpu is True else cpu
+        val, done, ms, nt, gbs = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=secs)
+        out["cpu_baseline"] = {"value": round(val, 3), "unit": "worker-steps/s", "cores": nt, "kind": "port",
+                               "sample": f"{done} full steps ({ms:.1f} ms each, {gbs:.0f} GB/s algorithmic) of the same workload within "
+                                         f"{secs:.0f} s; substitute CPU reference (oracle/ps_oracle.c, OpenMP)"}
+        if cpu is True:
+            v1, d1, ms1, _, g1 = cpu_run(label, sizes, S, W, opt, 10 ** 6, 1, seconds=secs / 4, threads=1)
+            out["cpu_baseline"]["single_thread"] = {"value": round(v1, 3), "ms_per_step": round(ms1, 1),
+                                                    "algorithmic_GBps": round(g1, 1), "steps": d1}
+    return out
 
+
+def brief(d, keys=("value", "unit", "ms_per_step", "ps_steps_per_sec", "roofline", "roofline_apply", "phases_ms", "cpu_baseline",
+                   "e2e", "gpu_launches", "steps")):
+    out = {k: d[k] for k in keys if d.get(k) is not None}
+    out["workload"] = d["config"]["workload"]
+    return out
+
+
+def main():
+    args = parse()
+    if args.workload == "c2":
+        return sparse_arm(args)
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    warm = max(args.warmup, 3)
+    parity = parity_check(args.workload, args, rank, world)
+    out = measure_dense(args.workload, args, rank, world, local, args.steps, warm, e2e=not args.no_e2e, cpu=not args.no_cpu)
+    out["parity_checked"] = parity
+    out.setdefault("cpu_baseline", None)
+    out.setdefault("e2e", None)
+    # ---- the other BASELINE configs, briefly, in the same process (not the headline) ----
+    also = {}
+    if not args.no_also:
+        n_also = max(10, min(args.steps, 30))
+        if args.workload != "c3":  # BASELINE configs[3]: ResNet-50-sized set at W = S = G
+            also["c3"] = brief(measure_dense("c3", args, rank, world, local, n_also, 3, cpu=(3.0 if world == 1 else False)))
+        if world == 1 and args.workload != "c0":  # BASELINE configs[0] (launch-bound: graph replay)
+            also["c0"] = brief(measure_dense("c0", args, rank, world, local, 200, 10, cpu=2.0, profile=False))
+        for kind in (("uniform", "zipf") if world == 1 else ("uniform",)):  # BASELINE configs[2] on N GPUs
+            also[f"c2_{kind}"] = brief(sparse_measure(args, kind, n_also, 3, e2e=False, cpu=(3.0 if world == 1 else False)),
+                                       keys=("value", "unit", "ms_per_step", "ps_steps_per_sec", "phases_ms", "roofline",
+                                             "roofline_apply", "cpu_baseline", "gpu_launches", "steps", "scaling"))
+    out["also"] = also or None
     if rank == 0:
-        out = {
-            "metric": "ps_steps_per_sec", "value": round(W * steps_per_s, 3), "unit": "worker-steps/s",
-            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 5),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": label, "shards": S, "workers": W, "optimizer": opt, "params_padded": ps.plan.P,
-                       "transport": args.transport if world > 1 else "local",
-                       "aggregate": (args.aggregate if world > 1 else "flat") + " fixed-order fold",
-                       "pipelined": bool(ps.overlap), "cuda_graph": bool(graphed),
-                       "l2": (f"inputs exceed L2 (per step each GPU streams {ps.algorithmic_bytes_per_step() / 1e9:.2f} GB "
-                              ">> 126 MB), no flush needed") if ps.algorithmic_bytes_per_step() > (512 << 20) else
-                             (f"working set ({ps.algorithmic_bytes_per_step() / 1e6:.0f} MB per step) fits the 126 MB L2 and is "
-                              "NOT flushed between steps: an L2-resident, launch-bound figure, not an HBM one")},
-            "ps_steps_per_sec": round(steps_per_s, 3), "host_enqueue_ms_per_step": round(host_ms, 4),
-            "algorithmic_GBps_per_gpu": round(ps.algorithmic_bytes_per_step() / ms_step / 1e6, 1),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        }
         print(json.dumps(out))
     if world > 1:
         dist.barrier()

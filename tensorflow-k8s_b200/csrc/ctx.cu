@@ -116,6 +116,7 @@ struct b200ps_ctx {
     cudaGraphExec_t graph = nullptr;
     struct GraphDel { void operator()(CUgraph_st* g) const { if (g) cudaGraphDestroy(g); } };
     std::unique_ptr<CUgraph_st, GraphDel> graph_src;  // kept alive: the node handles below belong to it
+    uint64_t graph_kernels = 0;  // kernel nodes of the graph (b200ps_launch_count counts them per replay)
     std::vector<cudaGraphNode_t> graph_adam_nodes;  // the apply nodes whose step size is re-armed per replay
     // profiling
     bool profile = false;
@@ -620,13 +621,18 @@ extern "C" int b200ps_dense_step(b200ps_ctx_t* c, void* stream) {
                 return rc;
             }
             B200PS_CUDA(e);
-            if (c->adam()) {  // the nodes whose step size changes every step
+            {
                 size_t n = 0;
                 cudaGraphGetNodes(g, nullptr, &n);
                 std::vector<cudaGraphNode_t> nodes(n);
                 if (n) cudaGraphGetNodes(g, nodes.data(), &n);
-                for (cudaGraphNode_t nd : nodes)
-                    if (dense_node_opt(nd) == OPT_ADAM) c->graph_adam_nodes.push_back(nd);
+                c->graph_kernels = 0;
+                for (cudaGraphNode_t nd : nodes) {
+                    cudaGraphNodeType ty;
+                    if (cudaGraphNodeGetType(nd, &ty) == cudaSuccess && ty == cudaGraphNodeTypeKernel) c->graph_kernels += 1;
+                    // the nodes whose step size changes every step
+                    if (c->adam() && dense_node_opt(nd) == OPT_ADAM) c->graph_adam_nodes.push_back(nd);
+                }
             }
             const cudaError_t e2 = cudaGraphInstantiate(&c->graph, g, 0);
             // the graph object must outlive the exec for node handles to stay meaningful: keep it until drop
@@ -637,6 +643,7 @@ extern "C" int b200ps_dense_step(b200ps_ctx_t* c, void* stream) {
             for (cudaGraphNode_t nd : c->graph_adam_nodes) B200PS_CUDA(dense_node_set_lr(c->graph, nd, lr_t));
         }
         B200PS_CUDA(cudaGraphLaunch(c->graph, st));
+        g_launches.fetch_add(c->graph_kernels, std::memory_order_relaxed);  // the kernels one replay launches
     } else {
         if (int rc = enqueue_step(c, st)) return rc;
     }
