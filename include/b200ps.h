@@ -175,6 +175,33 @@ int b200ps_linreg_grad(float* d_grad, const float* d_params, uint64_t n, int bat
                        void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * MLP worker group: the compute tasks of BASELINE configs[1] on the GPU.
+ * Reference: none -- the user's TensorFlow program in the WORKER containers (k8s-operator.md:6).
+ * Forward and backward of a dense MLP (ReLU between layers, linear output, loss 1/(2B) sum ||y - t||^2)
+ * for ALL compute tasks placed on this GPU; each task's fp32 gradient is written straight into its
+ * gradient buffer of the PS arena (zero-copy push), the fp32 parameters are read from the replica
+ * (zero-copy pull).  Mixed precision: bf16 operands, fp32 accumulation on the tcgen05 tensor cores
+ * (csrc/gemm_sm100.cuh: TMA loads, TMEM accumulators), fp32 gradients.  The variables are laid out
+ * as synth.mlp_c1_variables does: W_0 [d_0][d_1], b_0 [d_1], W_1, b_1, ...
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200ps_mlp b200ps_mlp_t;
+/* dims: d_0 .. d_L (multiples of 128); var_offsets: 2 L offsets (W_l, b_l) into the flat buffers, as
+ * b200ps_shard_map_var_offset gives them; batch_per_task a multiple of 64; 1..8 local tasks */
+int b200ps_mlp_create(const int* dims, int n_dims, int batch_per_task, int local_tasks, const uint64_t* var_offsets,
+                      b200ps_mlp_t** out);
+int b200ps_mlp_destroy(b200ps_mlp_t* mlp);
+/* One training step of the local tasks: h_x = features bf16 [tasks * batch][d_0] and h_t = targets bf16
+ * [tasks * batch][d_L] in pinned host memory (the mini-batches; copied to the device on `stream`),
+ * d_params = the replica, d_grads[i] = gradient buffer of the i-th local task; h_loss (may be NULL)
+ * receives one loss per task (device -> host on `stream`).  Asynchronous. */
+int b200ps_mlp_step(b200ps_mlp_t* mlp, const float* d_params, float* const* d_grads, const void* h_x, const void* h_t,
+                    float* h_loss, void* stream);
+/* The worker's GEMM on its own, for tests and roofline measurements: C[M][N] (bf16) = A[M][K] * B[N][K]^T,
+ * bf16 row-major device buffers, fp32 accumulation; d_ct (may be NULL) receives C^T.  M, N multiples of
+ * 128, K a multiple of 64. */
+int b200ps_gemm_bf16(const void* d_a, const void* d_b, void* d_c, void* d_ct, int M, int N, int K, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Transport group: buffers other ranks of the box can address.  Reference: none -- TensorFlow's
  * gRPC tensor transport between the PS and WORKER tasks of k8s-operator.md:6.  One process per
  * GPU; each rank exports its gradient / parameter arena, every peer maps it, and the step kernel

@@ -86,6 +86,10 @@ SIGNATURES = {
     "b200ps_launch_count": (_u64, []),
     "b200ps_linreg_scratch_bytes": (_sz, [_u64, _i32]),
     "b200ps_linreg_grad": (_i32, [_vp, _vp, _u64, _i32, _u64, _u64, _u64, _u64, _vp, _sz, _vp]),
+    "b200ps_mlp_create": (_i32, [_vp, _i32, _i32, _i32, _vp, _pp]),
+    "b200ps_mlp_destroy": (_i32, [_vp]),
+    "b200ps_mlp_step": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200ps_gemm_bf16": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp]),
     "b200ps_dev_alloc": (_i32, [_sz, _pp]),
     "b200ps_dev_free": (_i32, [_vp]),
     "b200ps_ipc_export": (_i32, [_vp, _vp]),
