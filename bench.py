@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the brief C3 / C0 / C2 measurements that ride along")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps, capped at 30")
+    ap.add_argument("--batch", type=int, default=512, help="mini-batch rows per compute task of the C1 worker (e2e leg)")
     return ap.parse_args()
 
 
@@ -630,32 +631,75 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
     # ---- end to end with HOST buffers ----
     if e2e:
         P = ps.plan.P
+        n_e2e = args.e2e_steps or min(steps, 30)
+
+        def timed_host_loop(fn, tail, n=None):
+            n = n or n_e2e
+            with torch.cuda.stream(stream):
+                for _ in range(5):
+                    fn()
+                sync()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(n):
+                    fn()
+                b.record()
+                tail()
+                sync()
+            return reduce_max(a.elapsed_time(b)) / n
+
+        # (1) host gradients: every worker's pinned host gradient in, pulled parameters out to one pinned host
+        #     replica per GPU (the workers of a GPU share it as they share the device replica)
         hg = {w: torch.empty(P, dtype=torch.float32).pin_memory() for w in ps.plan.local_workers}
-        # pull: one pinned host replica per GPU, shared by the workers placed on it (as they share the device replica)
         ho = {ps.plan.local_workers[0]: torch.empty(P, dtype=torch.float32).pin_memory()} if ps.plan.local_workers else {}
         for w in hg:
             hg[w].copy_(ps.grad_buffer(w))
         sync()
-        n_e2e = args.e2e_steps or min(steps, 30)
-        with torch.cuda.stream(stream):
-            for _ in range(3):
-                ps.step_host(hg, ho)
-            sync()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            for _ in range(n_e2e):
-                ps.step_host(hg, ho)
-            b.record()
-            ps.host_sync()
-            sync()
-        e_ms = reduce_max(a.elapsed_time(b)) / n_e2e
-        out["e2e"] = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
-                      "d2h_bytes_per_step": 4 * P * world, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
-                      "ps_steps_per_sec": round(1e3 / e_ms, 3),
-                      "pcie_bound_ms": round(4 * P * len(ps.plan.local_workers) / 55e6, 2),
-                      "api": "b200ps_dense_step_host via b200ps.ParameterServer.step_host (every worker's pinned host gradient in, "
-                             "pulled parameters out to one pinned host replica per GPU; chunk-pipelined inside the library)"}
+        e_ms = timed_host_loop(lambda: ps.step_host(hg, ho), ps.host_sync)
+        host_grad = {"value": round(W * 1e3 / e_ms, 3), "unit": "worker-steps/s", "h2d_bytes_per_step": 4 * P * W,
+                     "d2h_bytes_per_step": 4 * P * world, "ms_per_step": round(e_ms, 3), "steps": n_e2e,
+                     "ps_steps_per_sec": round(1e3 / e_ms, 3),
+                     "pcie_bound_ms": round(4 * P * len(ps.plan.local_workers) / 55e6, 2),
+                     "api": "b200ps_dense_step_host via b200ps.ParameterServer.step_host (every worker's pinned host gradient in, "
+                            "pulled parameters out to one pinned host replica per GPU; chunk-pipelined inside the library)"}
         del hg, ho
+        out["e2e"] = host_grad
+        if name == "c1":
+            # (2) the training step a user runs: the compute tasks are GPU tasks (b200ps_mlp_step: hand-written
+            #     tcgen05 GEMMs), so the host input of a step is the mini-batch; gradients never cross PCIe
+            from b200ps.worker import C1_DIMS, MlpWorker
+
+            ps.init_uniform(1)
+            ps.replica.mul_(0.02)  # weights of a trainable scale (u(-1, 1) * 0.02)
+            wk = MlpWorker(ps, C1_DIMS, args.batch)
+            gen = torch.Generator().manual_seed(7 + rank)
+            hx = torch.randn(wk.rows, C1_DIMS[0], generator=gen).bfloat16().pin_memory()
+            ht = torch.randn(wk.rows, C1_DIMS[-1], generator=gen).bfloat16().pin_memory()
+
+            def train_step():
+                wk.step(hx, ht)  # H2D of the mini-batches, forward/backward of the local tasks, loss D2H
+                ps.step()        # push (zero-copy) + aggregate + apply + pull (zero-copy)
+
+            smp = ClockSampler(local)
+            smp.start()
+            n_train = args.e2e_steps or min(steps, 100)
+            t_ms = timed_host_loop(train_step, lambda: None, n_train)
+            e2e_clocks = smp.finish()
+            w_ms = timed_host_loop(lambda: wk.step(hx, ht), lambda: None)  # the worker half alone, for the breakdown
+            losses = [float(v) for v in wk.loss]
+            out["e2e"] = {"value": round(W * 1e3 / t_ms, 3), "unit": "worker-steps/s",
+                          "h2d_bytes_per_step": 2 * wk.rows * (C1_DIMS[0] + C1_DIMS[-1]) * world,
+                          "d2h_bytes_per_step": 4 * len(wk.tasks) * world, "ms_per_step": round(t_ms, 3), "steps": n_train,
+                          "ps_steps_per_sec": round(1e3 / t_ms, 3), "batch_per_task": args.batch,
+                          "worker_TFLOPs_per_gpu": round(wk.flops_per_step() / t_ms / 1e9, 1),
+                          "loss_of_last_step": [round(v, 3) for v in losses], "worker_only_ms": round(w_ms, 3),
+                          "clocks": e2e_clocks,
+                          "api": "b200ps_mlp_step + b200ps_dense_step (b200ps.MlpWorker.step, ParameterServer.step): per step the "
+                                 "mini-batches of the local compute tasks go H2D from pinned memory, the tasks' forward/backward "
+                                 "runs on the GPU (bf16 tcgen05 GEMMs, fp32 gradients written into the PS arena), the fused PS "
+                                 "step follows, one loss per task comes back D2H",
+                          "host_gradients": host_grad}
+            wk.close()
     ps.close()
     del ps
     torch.cuda.empty_cache()

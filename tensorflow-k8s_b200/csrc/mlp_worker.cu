@@ -76,17 +76,38 @@ int launch_gemm(const CUtensorMap& a, const CUtensorMap& b, const gemm::Args& g,
     return B200PS_OK;
 }
 
-// fp32 W [rows][cols] -> bf16 W [rows][cols] and bf16 W^T [cols][rows] (32 x 32 tiles through shared memory)
-__global__ void cast_transpose_kernel(const float* __restrict__ w, bf16* __restrict__ wb, bf16* __restrict__ wbt, int rows, int cols) {
-    __shared__ float tile[32][33];
-    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
-    for (int i = threadIdx.y; i < 32; i += 8) {
-        const float x = w[(size_t)(r0 + i) * cols + c0 + threadIdx.x];
-        tile[i][threadIdx.x] = x;
-        wb[(size_t)(r0 + i) * cols + c0 + threadIdx.x] = __float2bfloat16_rn(x);
+// fp32 W [rows][cols] -> bf16 W [rows][cols] and bf16 W^T [cols][rows]: 64 x 64 tiles through shared memory,
+// 128-bit loads, 64-bit bf16x4 stores in both layouts (rows, cols multiples of 64)
+__global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __restrict__ w, bf16* __restrict__ wb, bf16* __restrict__ wbt,
+                                                             int rows, int cols) {
+    __shared__ float tile[64][65];
+    const int c0 = blockIdx.x * 64, r0 = blockIdx.y * 64;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // 16 threads x 4 elements per row, 16 rows per pass
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int r = ty + 16 * p;
+        const float4 x = __ldg(reinterpret_cast<const float4*>(w + (size_t)(r0 + r) * cols + c0) + tx);
+        tile[r][4 * tx + 0] = x.x;
+        tile[r][4 * tx + 1] = x.y;
+        tile[r][4 * tx + 2] = x.z;
+        tile[r][4 * tx + 3] = x.w;
+        __nv_bfloat162 lo = __floats2bfloat162_rn(x.x, x.y), hi = __floats2bfloat162_rn(x.z, x.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *(reinterpret_cast<uint2*>(wb + (size_t)(r0 + r) * cols + c0) + tx) = o;
     }
     __syncthreads();
-    for (int i = threadIdx.y; i < 32; i += 8) wbt[(size_t)(c0 + i) * rows + r0 + threadIdx.x] = __float2bfloat16_rn(tile[threadIdx.x][i]);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int c = ty + 16 * p;  // output row of W^T
+        __nv_bfloat162 lo = __floats2bfloat162_rn(tile[4 * tx + 0][c], tile[4 * tx + 1][c]);
+        __nv_bfloat162 hi = __floats2bfloat162_rn(tile[4 * tx + 2][c], tile[4 * tx + 3][c]);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *(reinterpret_cast<uint2*>(wbt + (size_t)(c0 + c) * rows + r0) + tx) = o;
+    }
 }
 
 // x [M][d] row-major -> xT [d][M]
@@ -173,6 +194,7 @@ struct b200ps_mlp {
     float* partial = nullptr;
     float* loss = nullptr;
     float** d_grad_ptrs = nullptr;       // device copy of the per-task gradient pointers
+    float* h_grad_ptrs[8] = {nullptr};   // what it holds
     // tensor maps: forward (A = H_l, B = W_l^T), dgrad (A = dH_l+1, B = W_l), wgrad (A = H_l^T, B = dH_l+1^T)
     std::vector<CUtensorMap> f_a, f_b, d_a, d_b, g_a, g_b;
     std::vector<int> f_bn, d_bn, g_bn;   // N tile per GEMM (256, or 128 when N is not a multiple of 256)
@@ -289,12 +311,17 @@ extern "C" int b200ps_mlp_step(b200ps_mlp_t* m, const float* d_params, float* co
     // the step's host inputs: the mini-batches of the local tasks (features and targets), H2D
     B200PS_CUDA(cudaMemcpyAsync(m->act[0], h_x, (size_t)M * d[0] * sizeof(bf16), cudaMemcpyHostToDevice, st));
     B200PS_CUDA(cudaMemcpyAsync(m->target, h_t, (size_t)M * d[L] * sizeof(bf16), cudaMemcpyHostToDevice, st));
-    B200PS_CUDA(cudaMemcpyAsync(m->d_grad_ptrs, d_grads, sizeof(float*) * (size_t)m->tasks, cudaMemcpyHostToDevice, st));
+    bool same = true;
+    for (int w = 0; w < m->tasks; ++w) same = same && m->h_grad_ptrs[w] == d_grads[w];
+    if (!same) {  // (a pageable source makes this copy synchronous: only when the buffers change)
+        for (int w = 0; w < m->tasks; ++w) m->h_grad_ptrs[w] = d_grads[w];
+        B200PS_CUDA(cudaMemcpyAsync(m->d_grad_ptrs, m->h_grad_ptrs, sizeof(float*) * (size_t)m->tasks, cudaMemcpyHostToDevice, st));
+    }
     const dim3 tb(32, 8);
     transpose_bf16_kernel<<<dim3(d[0] / 32, M / 32), tb, 0, st>>>(m->act[0], m->actT[0], M, d[0]);
     // pull: the workers read the replica -- once per GPU, cast to the bf16 operand layouts
     for (int l = 0; l < L; ++l)
-        cast_transpose_kernel<<<dim3(d[l + 1] / 32, d[l] / 32), tb, 0, st>>>(d_params + m->w_off[l], m->wb[l], m->wbt[l], d[l], d[l + 1]);
+        cast_transpose_kernel<<<dim3(d[l + 1] / 64, d[l] / 64), 256, 0, st>>>(d_params + m->w_off[l], m->wb[l], m->wbt[l], d[l], d[l + 1]);
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1 + (uint64_t)L, std::memory_order_relaxed);
     // forward
