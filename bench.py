@@ -44,7 +44,7 @@ def parse():
                     help="--workload c2 only: cross-rank barrier of the sparse step when N > 1")
     ap.add_argument("--overlap", action="store_true",
                     help="N > 1: pipeline the local folds with the NVLink exchange over two streams (helps at N=2, not at N=8)")
-    ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"],
+    ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level", "multimem"],
                     help="fold order over workers when N > 1 (identical on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true")

@@ -27,6 +27,7 @@
 #include "cuda_util.h"
 #include "dense_internal.h"
 #include "plan.h"
+#include "vmm.h"
 
 namespace b200ps {
 namespace {
@@ -40,9 +41,11 @@ constexpr long long SPIN_LIMIT = 8000000000ll;  // ~4 s at 2 GHz: a peer died or
 // What a kernel needs that changes from step to step, in device memory, so that a captured graph
 // stays valid: the barrier epoch and the abort word.
 struct DevState {
-    uint32_t epoch;
+    uint32_t epoch;       // barrier epoch
     uint32_t abort;
-    uint32_t pad[2];
+    uint32_t step_epoch;  // pipelined steps completed (advanced by the step's closing barrier): what the apply kernels wait for, minus 1
+    uint32_t fold_epoch;  // pipelined folds completed (advanced by the fold kernel): what it publishes, minus 1
+    uint32_t done[MAX_SLICES];  // arrival counters of the publishing fold kernel
 };
 
 struct BarrierArgs {
@@ -50,6 +53,7 @@ struct BarrierArgs {
     DevState* st;
     uint32_t* host_abort;  // mapped pinned host word: lets the host see a time-out without synchronising
     int rank, world;
+    int advance_step;  // 1: this barrier closes a pipelined step
 };
 
 // Arriving at its next barrier, rank r stores the new epoch into slot r of EVERY rank's flag array
@@ -64,6 +68,7 @@ __global__ void ctx_barrier_kernel(const __grid_constant__ BarrierArgs a) {
         const uint32_t e = a.st->epoch + 1;
         a.st->epoch = e;
         epoch_sh = e;
+        if (a.advance_step) a.st->step_epoch += 1;
     }
     __syncthreads();
     const uint32_t epoch = epoch_sh;
@@ -102,11 +107,21 @@ struct b200ps_ctx {
     float* arena = nullptr;    // own allocation (arena_elems + FLAG_WORDS words)
     float* base[MAX_RANKS] = {nullptr};  // base[r] = rank r's arena as mapped here
     bool imported = false;
+    // B200PS_AGG_MULTIMEM: the arena is a VMM allocation, replica + partial sum are bound to a multicast object
+    bool multimem = false;
+    vmm::Block vm_own;
+    vmm::Block vm_peer[MAX_RANKS];
+    vmm::Multicast mc;
+    std::unique_ptr<vmm::FdServer> fd_server;
+    std::string peer_server[MAX_RANKS];
+    size_t vm_bytes = 0, mc_bytes = 0;
     std::vector<float*> s1, s2;  // per launch: optimizer state of the local shard
     DevState* st = nullptr;
     uint32_t* host_abort = nullptr;      // pinned, mapped
     uint32_t* host_abort_dev = nullptr;  // its device alias
-    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr, s_fold = nullptr;
+    cudaEvent_t ev_fold = nullptr;
+    bool pipelined = false;  // two-level folds published slice by slice, applies waiting in their prologue
     std::vector<cudaEvent_t> ev_in, ev_k, ev_out;  // per chunk of step_host
     std::vector<char> ev_out_valid;
     cudaEvent_t ev_join = nullptr, ev_d2h = nullptr, ev_fork = nullptr;
@@ -137,9 +152,10 @@ int check_alive(const b200ps_ctx* c) {
     return B200PS_OK;
 }
 
-int need_peers(const b200ps_ctx* c) {
+int need_peers(b200ps_ctx* c) {
     B200PS_REQUIRE(c->plan->world == 1 || c->imported, B200PS_ERR_STATE,
                    "world = %d: call b200ps_ctx_import_handles before using the context", c->plan->world);
+    if (c->multimem && !c->mc.bound) return vmm::mc_bind_and_map(&c->mc, c->device, c->vm_own);
     return B200PS_OK;
 }
 
@@ -193,7 +209,7 @@ struct Mark {
     }
 };
 
-int barrier(b200ps_ctx* c, cudaStream_t st) {
+int barrier(b200ps_ctx* c, cudaStream_t st, bool advance_step = false) {
     const auto& p = *c->plan;
     if (p.world == 1) return B200PS_OK;
     Mark m(c, 2, st);
@@ -203,6 +219,7 @@ int barrier(b200ps_ctx* c, cudaStream_t st) {
     a.host_abort = c->host_abort_dev;
     a.rank = p.rank;
     a.world = p.world;
+    a.advance_step = advance_step ? 1 : 0;
     ctx_barrier_kernel<<<1, 32, 0, st>>>(a);
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -212,7 +229,7 @@ int barrier(b200ps_ctx* c, cudaStream_t st) {
 // One kernel over elements [lo, hi) of launch i's slice (flat-buffer coordinates).  `only_src` >= 0
 // folds just that one source (ordered-async mode); mirrors can be suppressed.
 int launch_apply(b200ps_ctx* c, size_t i, uint64_t lo, uint64_t hi, uint64_t t_step, cudaStream_t st, int only_src = -1,
-                 bool mirrors = true, float inv_w_override = 0.f) {
+                 bool mirrors = true, float inv_w_override = 0.f, int wait_unit = -1) {
     const auto& p = *c->plan;
     const auto& L = p.launches[i];
     if (hi <= lo) return B200PS_OK;
@@ -225,6 +242,51 @@ int launch_apply(b200ps_ctx* c, size_t i, uint64_t lo, uint64_t hi, uint64_t t_s
     }
     if (mirrors)
         for (int r : L.mirrors) mir[nm++] = c->base[r] + lo;
+    if (c->multimem && only_src < 0) {
+        McApply a;
+        float* mc = reinterpret_cast<float*>(c->mc.va);
+        a.g_mc = mc + p.P + lo;  // the partial-sum buffers sit behind the replicas in every arena
+        a.p_mc = mc + lo;
+        a.p = c->arena + lo;
+        a.n = hi - lo;
+        a.inv_w = c->inv_w;
+        a.abort_word = &c->st->abort;
+        if (wait_unit >= 0) {
+            a.wait_flags = c->flags_of(p.rank) + B200PS_BARRIER_WORDS + wait_unit * SLICE_FLAG_STRIDE;
+            a.wait_epoch = &c->st->step_epoch;
+            a.abort_out = &c->st->abort;
+            a.wait_mask = (1u << p.world) - 1u;
+        }
+        const uint64_t so = lo - L.begin;
+        a.m = c->s1[i] ? c->s1[i] + so : nullptr;
+        a.v = c->s2[i] ? c->s2[i] + so : nullptr;
+        switch (c->o.optimizer) {
+            case B200PS_OPT_ADAM:
+                a.opt = OPT_ADAM;
+                a.lr = lr_for_step(c, t_step);
+                a.beta1 = c->adam_c.beta1;
+                a.beta2 = c->adam_c.beta2;
+                a.omb1 = c->adam_c.omb1;
+                a.omb2 = c->adam_c.omb2;
+                a.eps = c->adam_c.eps;
+                break;
+            case B200PS_OPT_MOMENTUM:
+                a.opt = OPT_MOMENTUM;
+                a.lr = (float)c->o.lr;
+                a.beta1 = (float)c->o.momentum;
+                break;
+            case B200PS_OPT_FTRL:
+                a.opt = OPT_FTRL;
+                a.lr = (float)c->o.lr;
+                a.beta1 = (float)c->o.ftrl_l1;
+                a.beta2 = 2.0f * (float)c->o.ftrl_l2;
+                break;
+            default:
+                a.opt = OPT_SGD;
+                a.lr = (float)c->o.lr;
+        }
+        return dense_launch_mc(a, wait_unit >= 0 ? 2 : 8, st);
+    }
     DenseLaunch d;
     d.p = c->arena + lo;
     d.grads = g;
@@ -234,6 +296,12 @@ int launch_apply(b200ps_ctx* c, size_t i, uint64_t lo, uint64_t hi, uint64_t t_s
     d.n = hi - lo;
     d.inv_w = inv_w_override != 0.f ? inv_w_override : c->inv_w;
     d.abort_word = &c->st->abort;
+    if (wait_unit >= 0) {  // the sources are published by the producing ranks' fold kernels (flags in this rank's arena)
+        d.wait_flags = c->flags_of(p.rank) + B200PS_BARRIER_WORDS + wait_unit * SLICE_FLAG_STRIDE;
+        d.wait_epoch = &c->st->step_epoch;
+        d.abort_out = &c->st->abort;
+        for (const auto& src : L.src) d.wait_mask |= 1u << src.first;
+    }
     const uint64_t off = lo - L.begin;
     switch (c->o.optimizer) {
         case B200PS_OPT_ADAM: {
@@ -287,8 +355,62 @@ int launch_fold(b200ps_ctx* c, uint64_t lo, uint64_t hi, cudaStream_t st) {
     return dense_launch(d, c->tune, st);
 }
 
+// Pipelined form of the step (G > 1, two-level): the fold kernel runs on its own stream and publishes
+// slice after slice; the apply kernels, launched at once on `st` with a smaller grid, wait in their
+// prologue for the slices they own.  One barrier closes the step: every replica holds every updated
+// slice, and every partial sum may be overwritten.
+int enqueue_step_pipelined(b200ps_ctx* c, cudaStream_t st) {
+    const auto& p = *c->plan;
+    // publish units: every slice is cut into C chunks, walked chunk-major (chunk 0 of every slice, then
+    // chunk 1, ...), so that every owner gets work early; at most 32 units keep the per-unit
+    // synchronisation (a fence and one atomic per CTA) small against the fold itself
+    const int C = p.S >= 32 ? 1 : (32 / p.S < 4 ? 32 / p.S : 4);
+    auto chunk_range = [&](int s, int k, uint64_t* lo, uint64_t* hi) {
+        const uint64_t b = p.slices[(size_t)s].first, e = p.slices[(size_t)s].second;
+        const uint64_t len = ((e - b + (uint64_t)C - 1) / (uint64_t)C + 1023) / 1024 * 1024;
+        *lo = b + (uint64_t)k * len < e ? b + (uint64_t)k * len : e;
+        *hi = *lo + len < e ? *lo + len : e;
+    };
+    B200PS_CUDA(cudaEventRecord(c->ev_fork, st));
+    B200PS_CUDA(cudaStreamWaitEvent(c->s_fold, c->ev_fork, 0));
+    if (!p.local_workers.empty()) {
+        FoldPublish f{};
+        for (int w : p.local_workers) f.g[f.W++] = c->arena + p.grad_offset(w).second;
+        f.out = c->arena + p.P;
+        for (int k = 0; k < C; ++k)
+            for (int s = 0; s < p.S; ++s) {
+                const int u = f.n_slices++;
+                chunk_range(s, k, &f.begin[u], &f.end[u]);
+                const int owner = b200ps_placement_gpu(s, p.world);
+                f.flag[u] = c->flags_of(owner) + B200PS_BARRIER_WORDS + u * SLICE_FLAG_STRIDE + p.rank;
+            }
+        f.done = c->st->done;
+        f.epoch = &c->st->fold_epoch;
+        f.abort_word = &c->st->abort;
+        if (int rc = dense_fold_publish(f, 2, c->s_fold)) return rc;
+    }
+    B200PS_CUDA(cudaEventRecord(c->ev_fold, c->s_fold));
+    // Both kernels must be resident together whatever order the streams start them in: per SM two fold CTAs
+    // (256 threads x 55 registers) and two apply CTAs (256 x <= 64 registers at unroll 1) fit the register file.
+    // The apply is NVLink-bound, so the small grid costs nothing.
+    Tuning keep = c->tune;
+    c->tune = Tuning{256, 2, 1};
+    int rc = B200PS_OK;
+    for (int k = 0; k < C && !rc; ++k)
+        for (size_t i = 0; i < p.launches.size() && !rc; ++i) {
+            uint64_t lo = 0, hi = 0;
+            chunk_range(p.launches[i].shard, k, &lo, &hi);
+            rc = launch_apply(c, i, lo, hi, c->t + 1, st, -1, true, 0.f, k * p.S + p.launches[i].shard);
+        }
+    c->tune = keep;
+    if (rc) return rc;
+    B200PS_CUDA(cudaStreamWaitEvent(st, c->ev_fold, 0));
+    return barrier(c, st, true);
+}
+
 int enqueue_step(b200ps_ctx* c, cudaStream_t st) {
     const auto& p = *c->plan;
+    if (c->pipelined && !c->profile) return enqueue_step_pipelined(c, st);
     {
         Mark m(c, 0, st);
         if (int rc = launch_fold(c, 0, p.P, st)) return rc;
@@ -360,8 +482,6 @@ extern "C" int b200ps_ctx_create(const b200ps_cluster_t* cluster, const b200ps_s
     B200PS_REQUIRE(o.optimizer >= B200PS_OPT_SGD && o.optimizer <= B200PS_OPT_FTRL, B200PS_ERR_INVALID, "unknown optimizer %d",
                    o.optimizer);
     B200PS_REQUIRE(o.lr > 0, B200PS_ERR_RANGE, "lr must be positive");
-    B200PS_REQUIRE(o.aggregate != B200PS_AGG_MULTIMEM, B200PS_ERR_INVALID,
-                   "B200PS_AGG_MULTIMEM is not available in this build of the context");
     const int S = b200ps_cluster_num_shards(cluster), W = b200ps_cluster_num_workers(cluster);
     B200PS_REQUIRE(S == b200ps_shard_map_nshards(map), B200PS_ERR_INVALID,
                    "the cluster has %d ps tasks but the shard map has %d shards", S, b200ps_shard_map_nshards(map));
@@ -387,7 +507,24 @@ extern "C" int b200ps_ctx_create(const b200ps_cluster_t* cluster, const b200ps_s
     B200PS_CUDA(cudaGetDevice(&c->device));
     const size_t words = (size_t)plan->arena_elems(rank) + FLAG_WORDS;
     B200PS_REQUIRE(words > FLAG_WORDS || plan->P == 0, B200PS_ERR_RANGE, "empty arena");
-    B200PS_CUDA(cudaMalloc(&c->arena, words * 4));
+    c->multimem = o.aggregate == B200PS_AGG_MULTIMEM && plan->two_level();
+    if (c->multimem) {
+        B200PS_CUDA(cudaFree(nullptr));  // the runtime's context is current before the driver calls
+        B200PS_REQUIRE(vmm::available(), B200PS_ERR_STATE,
+                       "B200PS_AGG_MULTIMEM needs NVSwitch multicast support (b200ps_multicast_supported() is 0 on this device)");
+        for (int r = 0; r < world; ++r)
+            B200PS_REQUIRE(plan->workers_on(r) > 0, B200PS_ERR_INVALID,
+                           "B200PS_AGG_MULTIMEM adds the partial sums of ALL GPUs in the switch: every GPU must host a compute task");
+        const size_t gran = vmm::granularity(c->device, (size_t)plan->P * 8, world);
+        c->mc_bytes = ((size_t)plan->P * 8 + gran - 1) / gran * gran;  // replica + partial sum
+        c->vm_bytes = (words * 4 + gran - 1) / gran * gran;
+        if (c->vm_bytes < c->mc_bytes) c->vm_bytes = c->mc_bytes;
+        if (int rc = vmm::alloc(c->device, c->vm_bytes, &c->vm_own)) return rc;
+        c->arena = reinterpret_cast<float*>(c->vm_own.va);
+        B200PS_CUDA(cudaMemset(c->arena, 0, c->vm_bytes));
+    } else {
+        B200PS_CUDA(cudaMalloc(&c->arena, words * 4));
+    }
     c->base[rank] = c->arena;
     B200PS_CUDA(cudaMemset(c->arena + plan->arena_elems(rank), 0, FLAG_WORDS * 4));
     B200PS_CUDA(cudaMalloc(&c->st, sizeof(DevState)));
@@ -406,6 +543,9 @@ extern "C" int b200ps_ctx_create(const b200ps_cluster_t* cluster, const b200ps_s
     }
     B200PS_CUDA(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
     B200PS_CUDA(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    B200PS_CUDA(cudaStreamCreateWithFlags(&c->s_fold, cudaStreamNonBlocking));
+    B200PS_CUDA(cudaEventCreateWithFlags(&c->ev_fold, cudaEventDisableTiming));
+    c->pipelined = o.pipeline_folds && plan->two_level() && plan->S <= MAX_SLICES && plan->world <= SLICE_FLAG_STRIDE;
     B200PS_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     B200PS_CUDA(cudaEventCreateWithFlags(&c->ev_d2h, cudaEventDisableTiming));
     B200PS_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
@@ -419,8 +559,14 @@ extern "C" int b200ps_ctx_destroy(b200ps_ctx_t* c) {
     if (!c) return B200PS_OK;
     cudaDeviceSynchronize();
     drop_graph(c);
-    for (int r = 0; r < MAX_RANKS; ++r)
-        if (c->base[r] && c->base[r] != c->arena) cudaIpcCloseMemHandle(c->base[r]);
+    if (c->multimem) {
+        if (c->fd_server) c->fd_server->stop();
+        vmm::mc_release(&c->mc);
+        for (int r = 0; r < MAX_RANKS; ++r) vmm::release(&c->vm_peer[r]);
+    } else {
+        for (int r = 0; r < MAX_RANKS; ++r)
+            if (c->base[r] && c->base[r] != c->arena) cudaIpcCloseMemHandle(c->base[r]);
+    }
     for (float* p : c->s1) cudaFree(p);
     for (float* p : c->s2) cudaFree(p);
     for (auto& v : {c->ev_in, c->ev_k, c->ev_out})
@@ -431,27 +577,94 @@ extern "C" int b200ps_ctx_destroy(b200ps_ctx_t* c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_out) cudaStreamDestroy(c->s_out);
+    if (c->s_fold) cudaStreamDestroy(c->s_fold);
+    if (c->ev_fold) cudaEventDestroy(c->ev_fold);
     cudaFree(c->st);
     cudaFreeHost(c->host_abort);
-    cudaFree(c->arena);
+    if (c->multimem)
+        vmm::release(&c->vm_own);
+    else
+        cudaFree(c->arena);
     delete c;
     return B200PS_OK;
 }
 
+namespace {
+
+// the 64-byte handle of a VMM arena: where its file descriptor can be fetched (csrc/vmm.cu)
+struct VmHandle {
+    char magic[4];  // "B2VM"
+    int32_t rank;
+    uint64_t bytes, mc_bytes;
+    char server[40];
+};
+static_assert(sizeof(VmHandle) <= B200PS_IPC_HANDLE_BYTES, "handle size");
+
+}  // namespace
+
 extern "C" int b200ps_ctx_export_handle(b200ps_ctx_t* c, void* handle_out) {
     B200PS_REQUIRE(c && handle_out, B200PS_ERR_INVALID, "null argument");
-    return b200ps_ipc_export(c->arena, handle_out);
+    if (!c->multimem) return b200ps_ipc_export(c->arena, handle_out);
+    B200PS_REQUIRE(!c->fd_server, B200PS_ERR_STATE, "the handle was already exported");
+    int arena_fd = -1, mc_fd = -1;
+    if (int rc = vmm::export_fd(c->vm_own, &arena_fd)) return rc;
+    if (c->plan->rank == 0)  // rank 0 creates the multicast object and serves its handle too
+        if (int rc = vmm::mc_create(c->plan->world, c->mc_bytes, &c->mc, &mc_fd)) return rc;
+    static std::atomic<int> counter{0};
+    char name[40];
+    snprintf(name, sizeof name, "b200ps-%ld-%d", (long)getpid(), counter.fetch_add(1));
+    c->fd_server = std::make_unique<vmm::FdServer>();
+    if (int rc = c->fd_server->start(name, arena_fd, mc_fd)) return rc;
+    VmHandle h{};
+    memcpy(h.magic, "B2VM", 4);
+    h.rank = c->plan->rank;
+    h.bytes = c->vm_bytes;
+    h.mc_bytes = c->mc_bytes;
+    snprintf(h.server, sizeof h.server, "%s", name);
+    memset(handle_out, 0, B200PS_IPC_HANDLE_BYTES);
+    memcpy(handle_out, &h, sizeof h);
+    return B200PS_OK;
 }
 
 extern "C" int b200ps_ctx_import_handles(b200ps_ctx_t* c, const void* handles) {
     B200PS_REQUIRE(c && (handles || c->plan->world == 1), B200PS_ERR_INVALID, "null argument");
     B200PS_REQUIRE(!c->imported, B200PS_ERR_STATE, "handles were already imported");
-    for (int r = 0; r < c->plan->world; ++r) {
-        if (r == c->plan->rank) continue;
-        void* p = nullptr;
-        if (int rc = b200ps_ipc_open((const char*)handles + (size_t)r * B200PS_IPC_HANDLE_BYTES, &p)) return rc;
-        c->base[r] = (float*)p;
+    const int world = c->plan->world, rank = c->plan->rank;
+    if (!c->multimem) {
+        for (int r = 0; r < world; ++r) {
+            if (r == rank) continue;
+            void* p = nullptr;
+            if (int rc = b200ps_ipc_open((const char*)handles + (size_t)r * B200PS_IPC_HANDLE_BYTES, &p)) return rc;
+            c->base[r] = (float*)p;
+        }
+        c->imported = true;
+        return B200PS_OK;
     }
+    for (int r = 0; r < world; ++r) {
+        VmHandle h;
+        memcpy(&h, (const char*)handles + (size_t)r * B200PS_IPC_HANDLE_BYTES, sizeof h);
+        B200PS_REQUIRE(memcmp(h.magic, "B2VM", 4) == 0 && h.rank == r && h.mc_bytes == c->mc_bytes, B200PS_ERR_INVALID,
+                       "handle %d is not the B200PS_AGG_MULTIMEM handle of rank %d of this job", r, r);
+        h.server[sizeof h.server - 1] = 0;
+        c->peer_server[r] = h.server;
+        if (r == rank) continue;
+        int fd = -1;
+        if (int rc = vmm::fetch_fd(c->peer_server[r], 'A', &fd)) return rc;
+        const int rc = vmm::import_fd(c->device, fd, (size_t)h.bytes, &c->vm_peer[r]);
+        close(fd);
+        if (rc) return rc;
+        c->base[r] = reinterpret_cast<float*>(c->vm_peer[r].va);
+    }
+    if (rank != 0) {
+        int fd = -1;
+        if (int rc = vmm::fetch_fd(c->peer_server[0], 'M', &fd)) return rc;
+        const int rc = vmm::mc_import(fd, c->mc_bytes, &c->mc);
+        close(fd);
+        if (rc) return rc;
+    }
+    // every rank adds its device now; the memory is bound at the first collective call, i.e. after the
+    // host barrier the caller places behind this function (binding needs every device to have been added)
+    if (int rc = vmm::mc_add_device(&c->mc, c->device)) return rc;
     c->imported = true;
     return B200PS_OK;
 }
@@ -520,18 +733,7 @@ extern "C" int b200ps_ctx_phase_ms(b200ps_ctx_t* c, float* fold_ms, float* apply
     return B200PS_OK;
 }
 
-extern "C" int b200ps_multicast_supported(void) {
-    // driver entry points are resolved through the runtime, so the library does not link libcuda
-    typedef int (*attr_fn)(int*, int, int);
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-    if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) return 0;
-    const int CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED_ = 132;
-    if (((attr_fn)fn)(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED_, dev) != 0) return 0;
-    return v ? 1 : 0;
-}
+extern "C" int b200ps_multicast_supported(void) { return vmm::available() ? 1 : 0; }
 
 // ---- parameters ---------------------------------------------------------------------------------
 extern "C" int b200ps_dense_init(b200ps_ctx_t* c, const float* h_params, void* stream) {

@@ -55,6 +55,11 @@ struct DenseParams {
     int load_kind;  // gradient loads: 0 = nc + L1 no-allocate + L2 evict-first, 1 = plain coherent ld.global
     int end_fence;  // 1: every thread ends with a system-scope fence (drains its peer stores inside the kernel)
     const uint32_t* abort_word;  // non-null and *abort_word != 0: a barrier of this context timed out -> do nothing
+    // pipelined step: the sources of this slice are published by the producing ranks' fold kernels
+    const uint32_t* wait_flags;  // non-null: local flag words, one per producing rank
+    const uint32_t* wait_epoch;  // device word: the flags must reach *wait_epoch + 1
+    uint32_t* abort_out;         // raised when the wait times out
+    uint32_t wait_mask;          // producing ranks
 };
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -95,8 +100,8 @@ __device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
 }
 
 // one element: g = inv_w * sum; optimizer update.  Same operation order as ps_dense_sgd / ps_dense_adam.
-template <int OPT>
-__device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const DenseParams& a, const float lr) {
+template <int OPT, typename PT>
+__device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, const PT& a, const float lr) {
     if (OPT == OPT_FOLD) {
         p = sum;
         return;
@@ -124,8 +129,8 @@ __device__ __forceinline__ void apply1(float sum, float& p, float& m, float& v, 
     }
 }
 
-template <int OPT>
-__device__ __forceinline__ void apply4(const float4& s, float4& p, float4& m, float4& v, const DenseParams& a, const float lr) {
+template <int OPT, typename PT>
+__device__ __forceinline__ void apply4(const float4& s, float4& p, float4& m, float4& v, const PT& a, const float lr) {
     apply1<OPT>(s.x, p.x, m.x, v.x, a, lr);
     apply1<OPT>(s.y, p.y, m.y, v.y, a, lr);
     apply1<OPT>(s.z, p.z, m.z, v.z, a, lr);
@@ -195,6 +200,29 @@ __device__ __forceinline__ void trip(const DenseParams& a, const float lr, uint6
 template <int OPT, int WT, int U>
 __global__ void dense_apply_kernel(const __grid_constant__ DenseParams a) {
     if (a.abort_word && *(const volatile uint32_t*)a.abort_word) return;  // never update from gradients that did not all arrive
+    if (a.wait_flags) {  // pipelined step: wait until every producing rank has published this slice's partial sum
+        __shared__ uint32_t dead;
+        if (threadIdx.x == 0) {
+            const uint32_t want = *(const volatile uint32_t*)a.wait_epoch + 1u;
+            uint32_t bad = 0;
+            for (int r = 0; r < 32 && !bad; ++r) {
+                if (!((a.wait_mask >> r) & 1u)) continue;
+                const volatile uint32_t* f = a.wait_flags + r;
+                const long long t0 = clock64();
+                while ((int32_t)(*f - want) < 0) {
+                    if (clock64() - t0 > 8000000000ll || *(const volatile uint32_t*)a.abort_word) {  // ~4 s: a producer died
+                        *(volatile uint32_t*)a.abort_out = 1u;
+                        bad = 1;
+                        break;
+                    }
+                }
+            }
+            __threadfence_system();  // acquire: the partial sums behind the flags
+            dead = bad;
+        }
+        __syncthreads();
+        if (dead) return;
+    }
     // the step size stays a kernel parameter (constant bank): reading it from device memory into a
     // register cost 4 % of the C1 step on B200 (0.619 -> 0.648 ms); graph replay re-arms the node instead
     const float lr = a.lr;
@@ -234,6 +262,128 @@ __global__ void fill_uniform_kernel(float* __restrict__ dst, uint64_t n, uint64_
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const uint32_t k = (uint32_t)(hash64(key, first + i) >> 40);
         dst[i] = __fsub_rn(__fmul_rn((float)k, 0x1p-23f), 1.0f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// B200PS_AGG_MULTIMEM: the G partial sums of a slice are added INSIDE the NVSwitch -- one
+// multimem.ld_reduce on the multicast mapping returns their sum, so 4 bytes per element arrive at the
+// owner instead of 4 (G - 1) -- and the updated slice reaches every replica (this GPU's included) with
+// one multimem.st.  The summation order is the switch's: checked against the oracle at 1e-6 relative.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 mc_ld_reduce(const float4* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void mc_st(float4* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <int OPT>
+__global__ void __launch_bounds__(256) dense_apply_mc_kernel(const __grid_constant__ McApply a) {
+    if (*(const volatile uint32_t*)a.abort_word) return;
+    if (a.wait_flags) {  // pipelined step: every rank has published its partial sum of this unit
+        __shared__ uint32_t dead;
+        if (threadIdx.x == 0) {
+            const uint32_t want = *(const volatile uint32_t*)a.wait_epoch + 1u;
+            uint32_t bad = 0;
+            for (int r = 0; r < 32 && !bad; ++r) {
+                if (!((a.wait_mask >> r) & 1u)) continue;
+                const volatile uint32_t* f = a.wait_flags + r;
+                const long long t0 = clock64();
+                while ((int32_t)(*f - want) < 0) {
+                    if (clock64() - t0 > 8000000000ll || *(const volatile uint32_t*)a.abort_word) {
+                        *(volatile uint32_t*)a.abort_out = 1u;
+                        bad = 1;
+                        break;
+                    }
+                }
+            }
+            __threadfence_system();
+            dead = bad;
+        }
+        __syncthreads();
+        if (dead) return;
+    }
+    const float lr = a.lr;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, n4 = a.n / 4;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
+        const bool two = i + stride < n4;
+        float4 s0 = mc_ld_reduce(reinterpret_cast<const float4*>(a.g_mc) + i), s1 = s0;
+        if (two) s1 = mc_ld_reduce(reinterpret_cast<const float4*>(a.g_mc) + i + stride);
+        float4 P0 = ld_state(reinterpret_cast<const float4*>(a.p) + i), P1 = P0, M0 = P0, M1 = P0, V0 = P0, V1 = P0;
+        if (HAS_M(OPT)) M0 = ld_state(reinterpret_cast<const float4*>(a.m) + i);
+        if (HAS_V(OPT)) V0 = ld_state(reinterpret_cast<const float4*>(a.v) + i);
+        if (two) {
+            P1 = ld_state(reinterpret_cast<const float4*>(a.p) + i + stride);
+            if (HAS_M(OPT)) M1 = ld_state(reinterpret_cast<const float4*>(a.m) + i + stride);
+            if (HAS_V(OPT)) V1 = ld_state(reinterpret_cast<const float4*>(a.v) + i + stride);
+        }
+        apply4<OPT>(s0, P0, M0, V0, a, lr);
+        mc_st(reinterpret_cast<float4*>(a.p_mc) + i, P0);
+        if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + i, M0);
+        if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + i, V0);
+        if (two) {
+            apply4<OPT>(s1, P1, M1, V1, a, lr);
+            mc_st(reinterpret_cast<float4*>(a.p_mc) + i + stride, P1);
+            if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + i + stride, M1);
+            if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + i + stride, V1);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Pipelined two-level aggregation: ONE fold kernel walks all S slices in order; when the last CTA has
+// finished slice s it publishes this rank's partial sum of s to the slice's owner (a flag word in the
+// owner's arena, a posted NVLink store), and the owner's apply kernel -- already resident, waiting in
+// its prologue -- starts on s while this kernel is folding s + 1.  HBM-bound fold and NVLink-bound
+// exchange overlap without extra launches.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dense_fold_publish_kernel(const __grid_constant__ FoldPublish f) {
+    if (*(const volatile uint32_t*)f.abort_word) return;
+    const uint64_t pol = policy_evict_first();
+    const uint32_t epoch = *(volatile uint32_t*)f.epoch + 1u;  // every CTA reads it before the last arrival of the last slice
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int s = 0; s < f.n_slices; ++s) {
+        const uint64_t b4 = f.begin[s] / 4, e4 = f.end[s] / 4;  // slices are 1024-element aligned
+        for (uint64_t i = b4 + tid; i < e4; i += 2 * stride) {
+            const bool two = i + stride < e4;
+            float4 a0 = ld_once(reinterpret_cast<const float4*>(f.g[0]) + i, pol), a1 = a0;
+            if (two) a1 = ld_once(reinterpret_cast<const float4*>(f.g[0]) + i + stride, pol);
+            for (int w0 = 1; w0 < f.W; w0 += 4) {
+                float4 x[4], y[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (w0 + c < f.W) {
+                        x[c] = ld_once(reinterpret_cast<const float4*>(f.g[w0 + c]) + i, pol);
+                        if (two) y[c] = ld_once(reinterpret_cast<const float4*>(f.g[w0 + c]) + i + stride, pol);
+                    }
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (w0 + c < f.W) {
+                        a0 = add4(a0, x[c]);
+                        if (two) a1 = add4(a1, y[c]);
+                    }
+            }
+            st_f4(reinterpret_cast<float4*>(f.out) + i, a0);
+            if (two) st_f4(reinterpret_cast<float4*>(f.out) + i + stride, a1);
+        }
+        __threadfence_system();  // this thread's part of the partial sum is visible to the peers
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const uint32_t arrived = atomicAdd(&f.done[s], 1u);
+            if (arrived == gridDim.x - 1) {  // last CTA of slice s
+                f.done[s] = 0;               // re-armed for the next step
+                __threadfence_system();
+                if (f.flag[s]) *(volatile uint32_t*)f.flag[s] = epoch;
+                if (s == f.n_slices - 1) *(volatile uint32_t*)f.epoch = epoch;  // every CTA has read the old value by now
+            }
+        }
     }
 }
 
@@ -318,7 +468,7 @@ int dense_apply(int opt, DenseParams& a, const float* const* d_grads, float* con
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     static const int env_load_kind = getenv("B200PS_DENSE_LOAD") ? atoi(getenv("B200PS_DENSE_LOAD")) : 0;  // experiments
-    a.load_kind = env_load_kind;
+    if (env_load_kind) a.load_kind = env_load_kind;
     static const int env_end_fence = getenv("B200PS_DENSE_END_FENCE") ? atoi(getenv("B200PS_DENSE_END_FENCE")) : 0;  // experiments
     a.end_fence = (env_end_fence && a.n_mirror > 0) ? 1 : 0;
     const uint64_t work = a.n4 ? a.n4 : a.n;
@@ -354,7 +504,45 @@ int dense_launch(const DenseLaunch& l, const Tuning& t, cudaStream_t stream) {
     a.omb2 = l.omb2;
     a.eps = l.eps;
     a.abort_word = l.abort_word;
+    a.wait_flags = l.wait_flags;
+    a.wait_epoch = l.wait_epoch;
+    a.wait_mask = l.wait_mask;
+    a.abort_out = l.abort_out;
+    a.load_kind = l.wait_flags ? 1 : 0;  // sources published during this kernel's lifetime are read with coherent loads
     return dense_apply(l.opt, a, l.grads, l.mirrors, (void*)stream, t);
+}
+
+int dense_launch_mc(const McApply& a, int ctas_per_sm, cudaStream_t stream) {
+    B200PS_REQUIRE(a.g_mc && a.p_mc && a.p && a.abort_word && a.n % 4 == 0 &&
+                       (((uintptr_t)a.g_mc | (uintptr_t)a.p_mc | (uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v) & 15) == 0,
+                   B200PS_ERR_INVALID, "bad multicast-apply arguments");
+    if (a.n == 0) return B200PS_OK;
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    const uint64_t want = (a.n / 4 + 511) / 512, cap = (uint64_t)sms * (uint64_t)ctas_per_sm;
+    const int grid = (int)(want < cap ? want : cap);
+    cudaStream_t st = stream;
+    switch (a.opt) {
+        case OPT_ADAM: dense_apply_mc_kernel<OPT_ADAM><<<grid, 256, 0, st>>>(a); break;
+        case OPT_MOMENTUM: dense_apply_mc_kernel<OPT_MOMENTUM><<<grid, 256, 0, st>>>(a); break;
+        case OPT_FTRL: dense_apply_mc_kernel<OPT_FTRL><<<grid, 256, 0, st>>>(a); break;
+        default: dense_apply_mc_kernel<OPT_SGD><<<grid, 256, 0, st>>>(a);
+    }
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
+}
+
+int dense_fold_publish(const FoldPublish& f, int ctas_per_sm, cudaStream_t stream) {
+    B200PS_REQUIRE(f.W >= 1 && f.W <= B200PS_MAX_WORKERS && f.n_slices >= 1 && f.n_slices <= 64 && f.out && f.done && f.epoch &&
+                       f.abort_word,
+                   B200PS_ERR_INVALID, "bad fold-publish arguments");
+    int sms = 0;
+    B200PS_CUDA(sm_count(&sms));
+    dense_fold_publish_kernel<<<sms * ctas_per_sm, 256, 0, stream>>>(f);
+    B200PS_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return B200PS_OK;
 }
 
 int dense_node_opt(cudaGraphNode_t node) {

@@ -6,6 +6,8 @@
 
 #include <cstdint>
 
+#include "b200ps.h"
+
 namespace b200ps {
 
 // FOLD: out[i] = left fold of the buffers, nothing else
@@ -33,7 +35,46 @@ struct DenseLaunch {
     float c1 = 0.f, c2 = 0.f;  // Adam beta1, beta2 | momentum, - | FTRL l1, 2*l2
     float omb1 = 0.f, omb2 = 0.f, eps = 0.f;
     const uint32_t* abort_word = nullptr;
+    // pipelined step: wait in the kernel's prologue until flags[r] >= *wait_epoch + 1 for every r in wait_mask
+    const uint32_t* wait_flags = nullptr;
+    const uint32_t* wait_epoch = nullptr;
+    uint32_t wait_mask = 0;
+    uint32_t* abort_out = nullptr;
 };
+
+// Apply of one slice in B200PS_AGG_MULTIMEM mode: the gradient sum comes from the multicast mapping of
+// the partial-sum buffers (added in the switch), the updated slice goes to every replica through the
+// multicast mapping of the replicas.  (Field names match DenseParams: the optimizer arithmetic is shared.)
+struct McApply {
+    int opt = OPT_SGD;
+    const float* g_mc = nullptr;  // multicast address of this slice in the partial-sum buffers
+    float* p_mc = nullptr;        // multicast address of this slice in the replicas
+    const float* p = nullptr;     // this GPU's replica (read)
+    float* m = nullptr;
+    float* v = nullptr;
+    uint64_t n = 0;
+    float inv_w = 1.f, lr = 0.f, beta1 = 0.f, beta2 = 0.f, omb1 = 0.f, omb2 = 0.f, eps = 0.f;
+    const uint32_t* abort_word = nullptr;
+    const uint32_t* wait_flags = nullptr;
+    const uint32_t* wait_epoch = nullptr;
+    uint32_t wait_mask = 0;
+    uint32_t* abort_out = nullptr;
+};
+int dense_launch_mc(const McApply& a, int ctas_per_sm, cudaStream_t stream);
+
+// One kernel folds every slice of the flat buffer in order and publishes each to its owner (see dense.cu).
+struct FoldPublish {
+    const float* g[B200PS_MAX_WORKERS];  // the local compute tasks' gradient buffers (whole flat buffer), worker order
+    int W;
+    float* out;                          // this GPU's partial-sum buffer (whole flat buffer)
+    int n_slices;
+    uint64_t begin[64], end[64];         // slice ranges (elements)
+    uint32_t* flag[64];                  // where slice s is published: the owner's flag word for this rank (local or peer)
+    uint32_t* done;                      // n_slices device counters, zero between steps
+    uint32_t* epoch;                     // device word: this step publishes *epoch + 1 and then stores it back
+    const uint32_t* abort_word;
+};
+int dense_fold_publish(const FoldPublish& f, int ctas_per_sm, cudaStream_t stream);
 
 int dense_launch(const DenseLaunch& l, const Tuning& t, cudaStream_t stream);
 

@@ -83,3 +83,19 @@ def test_peer_memory_barrier():
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
     _run(2, 3, 5, "adam", "peer", "flat", "sequential", "peer")
+
+
+@pytest.mark.parametrize("S,W,opt,mode", [(4, 8, "adam", "sequential"), (2, 2, "sgd", "sequential"), (4, 8, "adam", "overlap")])
+def test_in_switch_reduction_matches_within_tolerance(S, W, opt, mode):
+    """B200PS_AGG_MULTIMEM: the per-GPU partial sums are added inside the NVSwitch (multimem.ld_reduce) and
+    the updated slices are multicast to every replica (multimem.st).  The switch picks the summation
+    order, so the check is the north-star tolerance (1e-6 relative), not bit-exactness."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import b200ps
+
+    torch.cuda.set_device(0)
+    if not b200ps._lib.lib.b200ps_multicast_supported():
+        pytest.skip("the device reports no multicast support")
+    _run(2, S, W, opt, "peer", "multimem", mode)
