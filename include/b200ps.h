@@ -361,7 +361,8 @@ int b200ps_sparse_push_sgd_noalloc(float* const* d_shard_base, const int64_t* co
  * ---------------------------------------------------------------------------------------------- */
 typedef struct b200ps_ctx b200ps_ctx_t;
 
-enum { B200PS_OPT_SGD = 0, B200PS_OPT_ADAM = 1, B200PS_OPT_MOMENTUM = 2, B200PS_OPT_FTRL = 3 };
+enum { B200PS_OPT_SGD = 0, B200PS_OPT_ADAM = 1, B200PS_OPT_MOMENTUM = 2, B200PS_OPT_FTRL = 3,
+       B200PS_OPT_ADAGRAD = 4 /* embedding tables only */ };
 enum { B200PS_AGG_FLAT = 0,      /* g = (1/W) * left fold over the workers in worker order (a6) */
        B200PS_AGG_TWO_LEVEL = 1, /* G > 1: every GPU folds its own workers (worker order), the owner
                                     folds the per-GPU partial sums in GPU order; same bits as FLAT on one GPU */
@@ -471,6 +472,67 @@ int b200ps_ctx_set_profile(b200ps_ctx_t* ctx, int on);
 int b200ps_ctx_phase_ms(b200ps_ctx_t* ctx, float* fold_ms, float* apply_ms, float* barrier_ms);
 /* 1 if the current device and driver support NVSwitch multicast objects (B200PS_AGG_MULTIMEM) */
 int b200ps_multicast_supported(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Table group: one embedding table of the job as an object the library owns (SURVEY.md 8(b) "sparse
+ * group"; rows a10..a12).  Reference: none -- TensorFlow's partitioned embedding variable on the PS
+ * tasks of k8s-operator.md:6, embedding_lookup and the sparse optimizer ops.
+ *
+ * Rows are partitioned by TF "div" over the cluster's PS shards; shard s lives on GPU s mod G,
+ * compute task w on GPU w mod G.  A rank's table object owns ONE arena, exported to the other ranks:
+ *   [ local shards | (Adagrad accumulators) | per local compute task: ids int64[B], gradient rows
+ *     [B, dim], pulled rows [B, dim] | per REMOTE compute task: staging [B, dim] | barrier words ]
+ * plus the push workspace.  Set-up for G > 1 is the context's: create -> export_handle -> (all-gather)
+ * -> import_handles -> (host barrier) -> calls ... -> (host barrier) -> destroy.  Workers write ids
+ * and gradient rows into their buffers (b200ps_table_worker_buffers) and read the pulled rows there.
+ * Collective calls (every rank, same order): b200ps_sparse_pull, b200ps_sparse_push, b200ps_sparse_step.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200ps_table b200ps_table_t;
+typedef struct {
+    int optimizer;     /* B200PS_OPT_SGD | B200PS_OPT_ADAGRAD */
+    int use_graph;     /* 1: b200ps_sparse_step replays one CUDA graph (captured on first use) */
+    double lr;
+    double accum_init; /* Adagrad: TF's initial_accumulator_value, 0.1 */
+} b200ps_table_options_t;
+int b200ps_table_options_default(b200ps_table_options_t* opt);
+
+/* The arena layout of rank `of_rank`, pure arithmetic (no device): byte offsets; entries that do not
+ * live on that rank are UINT64_MAX.  Arrays: num_shards (shard, accum), num_workers (ids, grad,
+ * pulled, staging -- the staging slot ON of_rank for a task placed elsewhere).  Any output may be NULL. */
+int b200ps_table_layout(uint64_t rows, int dim, int num_shards, int num_workers, uint64_t ids_per_worker, int world,
+                        int adagrad, int of_rank, uint64_t* arena_bytes, uint64_t* flag_offset, uint64_t* shard_offset,
+                        uint64_t* accum_offset, uint64_t* ids_offset, uint64_t* grad_offset, uint64_t* pulled_offset,
+                        uint64_t* staging_offset);
+
+int b200ps_table_create(const b200ps_cluster_t* cluster, uint64_t rows, int dim, uint64_t ids_per_worker, int rank,
+                        int world, const b200ps_table_options_t* opt, b200ps_table_t** out);
+int b200ps_table_destroy(b200ps_table_t* table);
+int b200ps_table_export_handle(b200ps_table_t* table, void* handle_out /* B200PS_IPC_HANDLE_BYTES */);
+int b200ps_table_import_handles(b200ps_table_t* table, const void* handles /* world * B200PS_IPC_HANDLE_BYTES */);
+int b200ps_table_sync(b200ps_table_t* table, void* stream); /* joins the stream, reports a barrier time-out */
+int b200ps_table_init_uniform(b200ps_table_t* table, uint64_t seed, void* stream); /* row i, column d = u(seed,0,0,i*dim+d) */
+/* device views: a local compute task's ids / gradient rows / pulled rows; a local shard's rows (and accumulators) */
+int b200ps_table_worker_buffers(b200ps_table_t* table, int worker, int64_t** d_ids, float** d_grad_rows, float** d_pulled);
+int b200ps_table_shard(b200ps_table_t* table, int shard, float** d_rows, float** d_accum, uint64_t* row_begin,
+                       uint64_t* row_end);
+/* a10 for every compute task of the job at once: afterwards the pulled buffer of every local task holds table[ids] */
+int b200ps_sparse_pull(b200ps_table_t* table, void* stream);
+/* a10 for one local task, rows read from the owning GPUs directly (not collective) */
+int b200ps_sparse_pull_worker(b200ps_table_t* table, int worker, float* d_out, void* stream);
+/* a11 + a12 for the shards of this GPU over every task's (ids, gradient rows) */
+int b200ps_sparse_push(b200ps_table_t* table, void* stream);
+/* pull of all tasks, then push, sharing one barrier */
+int b200ps_sparse_step(b200ps_table_t* table, void* stream);
+int b200ps_table_set_graph(b200ps_table_t* table, int on);
+int b200ps_table_set_profile(b200ps_table_t* table, int on);
+int b200ps_table_phase_ms(b200ps_table_t* table, float* serve_ms, float* route_sort_ms, float* apply_ms);
+/* the plan of the last push (see b200ps_sparse_plan_read) */
+int b200ps_table_plan_read(b200ps_table_t* table, uint64_t* n_kept, uint64_t* n_unique, uint64_t* n_bad,
+                           int64_t* h_sorted_ids, uint32_t* h_perm, int32_t* h_seg_id, int64_t* h_unique_ids,
+                           uint32_t* h_seg_offset, void* stream);
+/* <directory>/table-rank<r>-of-<G>.b200ps: this rank's shards (and accumulators); temporary file + rename */
+int b200ps_table_save(b200ps_table_t* table, const char* directory, void* stream);
+int b200ps_table_load(b200ps_table_t* table, const char* directory, void* stream);
 
 #ifdef __cplusplus
 }

@@ -36,7 +36,13 @@ class DenseOptions(C.Structure):
                 ("unroll", C.c_int), ("use_graph", C.c_int), ("pipeline_folds", C.c_int), ("host_chunk_elems", C.c_uint64)]
 
 
-OPT_SGD, OPT_ADAM, OPT_MOMENTUM, OPT_FTRL = 0, 1, 2, 3
+OPT_SGD, OPT_ADAM, OPT_MOMENTUM, OPT_FTRL, OPT_ADAGRAD = 0, 1, 2, 3, 4
+
+
+class TableOptions(C.Structure):
+    """b200ps_table_options_t"""
+    _fields_ = [("optimizer", C.c_int), ("use_graph", C.c_int), ("lr", C.c_double), ("accum_init", C.c_double)]
+
 AGG_FLAT, AGG_TWO_LEVEL, AGG_MULTIMEM = 0, 1, 2
 
 OK, ERR_INVALID, ERR_PARSE, ERR_VALIDATION, ERR_CUDA, ERR_RANGE, ERR_STATE = 0, -1, -2, -3, -4, -5, -6
@@ -151,6 +157,28 @@ SIGNATURES = {
     "b200ps_ctx_set_profile": (_i32, [_vp, _i32]),
     "b200ps_ctx_phase_ms": (_i32, [_vp, C.POINTER(_f32), C.POINTER(_f32), C.POINTER(_f32)]),
     "b200ps_multicast_supported": (_i32, []),
+    # table group
+    "b200ps_table_options_default": (_i32, [C.POINTER(TableOptions)]),
+    "b200ps_table_layout": (_i32, [_u64, _i32, _i32, _i32, _u64, _i32, _i32, _i32, C.POINTER(_u64), C.POINTER(_u64), _vp, _vp, _vp, _vp,
+                                    _vp, _vp]),
+    "b200ps_table_create": (_i32, [_vp, _u64, _i32, _u64, _i32, _i32, C.POINTER(TableOptions), _pp]),
+    "b200ps_table_destroy": (_i32, [_vp]),
+    "b200ps_table_export_handle": (_i32, [_vp, _vp]),
+    "b200ps_table_import_handles": (_i32, [_vp, _vp]),
+    "b200ps_table_sync": (_i32, [_vp, _vp]),
+    "b200ps_table_init_uniform": (_i32, [_vp, _u64, _vp]),
+    "b200ps_table_worker_buffers": (_i32, [_vp, _i32, _pp, _pp, _pp]),
+    "b200ps_table_shard": (_i32, [_vp, _i32, _pp, _pp, C.POINTER(_u64), C.POINTER(_u64)]),
+    "b200ps_sparse_pull": (_i32, [_vp, _vp]),
+    "b200ps_sparse_pull_worker": (_i32, [_vp, _i32, _vp, _vp]),
+    "b200ps_sparse_push": (_i32, [_vp, _vp]),
+    "b200ps_sparse_step": (_i32, [_vp, _vp]),
+    "b200ps_table_set_graph": (_i32, [_vp, _i32]),
+    "b200ps_table_set_profile": (_i32, [_vp, _i32]),
+    "b200ps_table_phase_ms": (_i32, [_vp, C.POINTER(_f32), C.POINTER(_f32), C.POINTER(_f32)]),
+    "b200ps_table_plan_read": (_i32, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64), _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200ps_table_save": (_i32, [_vp, _cp, _vp]),
+    "b200ps_table_load": (_i32, [_vp, _cp, _vp]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -18,6 +18,7 @@
 #include <cerrno>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -26,17 +27,17 @@
 #include "common.h"
 #include "cuda_util.h"
 #include "dense_internal.h"
+#include "peer_sync.cuh"
 #include "plan.h"
 #include "vmm.h"
 
 namespace b200ps {
 namespace {
 
-constexpr int MAX_RANKS = B200PS_MAX_MIRRORS + 1;
+constexpr int MAX_RANKS = SYNC_MAX_RANKS;
 constexpr int SLICE_FLAG_STRIDE = 16;  // words per slice in the slice-ready flags: one per producing rank
 constexpr int MAX_SLICES = 64;
 constexpr int FLAG_WORDS = B200PS_BARRIER_WORDS + MAX_SLICES * SLICE_FLAG_STRIDE;  // behind every arena
-constexpr long long SPIN_LIMIT = 8000000000ll;  // ~4 s at 2 GHz: a peer died or never arrived
 
 // What a kernel needs that changes from step to step, in device memory, so that a captured graph
 // stays valid: the barrier epoch and the abort word.
@@ -47,46 +48,6 @@ struct DevState {
     uint32_t fold_epoch;  // pipelined folds completed (advanced by the fold kernel): what it publishes, minus 1
     uint32_t done[MAX_SLICES];  // arrival counters of the publishing fold kernel
 };
-
-struct BarrierArgs {
-    uint32_t* flags[MAX_RANKS];  // flags[r] = rank r's barrier words (local or peer pointer)
-    DevState* st;
-    uint32_t* host_abort;  // mapped pinned host word: lets the host see a time-out without synchronising
-    int rank, world;
-    int advance_step;  // 1: this barrier closes a pipelined step
-};
-
-// Arriving at its next barrier, rank r stores the new epoch into slot r of EVERY rank's flag array
-// (posted NVLink stores) and waits until all slots of its OWN array have reached it.  The kernels
-// queued before it on the stream have completed, so their peer stores are performed; the
-// system-scope fences order the flag traffic itself.  Every rank runs on its own GPU, so a waiting
-// kernel never waits for a kernel that needs the same GPU.
-__global__ void ctx_barrier_kernel(const __grid_constant__ BarrierArgs a) {
-    __shared__ uint32_t epoch_sh;
-    const int t = threadIdx.x;
-    if (t == 0) {
-        const uint32_t e = a.st->epoch + 1;
-        a.st->epoch = e;
-        epoch_sh = e;
-        if (a.advance_step) a.st->step_epoch += 1;
-    }
-    __syncthreads();
-    const uint32_t epoch = epoch_sh;
-    if (t < a.world && !a.st->abort) {
-        __threadfence_system();
-        *(volatile uint32_t*)(a.flags[t] + a.rank) = epoch;  // my arrival, in rank t's array
-        const volatile uint32_t* mine = a.flags[a.rank] + t;
-        const long long t0 = clock64();
-        while ((int32_t)(*mine - epoch) < 0) {  // epochs only grow; the signed difference tolerates wrap-around
-            if (clock64() - t0 > SPIN_LIMIT) {
-                a.st->abort = 1u;
-                *(volatile uint32_t*)a.host_abort = 1u;
-                break;
-            }
-        }
-        __threadfence_system();
-    }
-}
 
 const char* opt_name(int o) {
     return o == B200PS_OPT_ADAM ? "adam" : o == B200PS_OPT_MOMENTUM ? "momentum" : o == B200PS_OPT_FTRL ? "ftrl" : "sgd";
@@ -138,6 +99,7 @@ struct b200ps_ctx {
     struct Span { cudaEvent_t a, b; };
     std::vector<Span> spans[3];  // fold, apply, barrier
     std::vector<cudaEvent_t> event_pool;
+    std::vector<cudaEvent_t> phase_ev;
 
     uint32_t* flags_of(int r) const { return reinterpret_cast<uint32_t*>(base[r] + plan->arena_elems(r)); }
     bool adam() const { return o.optimizer == B200PS_OPT_ADAM; }
@@ -213,14 +175,15 @@ int barrier(b200ps_ctx* c, cudaStream_t st, bool advance_step = false) {
     const auto& p = *c->plan;
     if (p.world == 1) return B200PS_OK;
     Mark m(c, 2, st);
-    BarrierArgs a{};
+    PeerBarrierArgs a{};
     for (int r = 0; r < p.world; ++r) a.flags[r] = c->flags_of(r);
-    a.st = c->st;
+    a.epoch = &c->st->epoch;
+    a.abort = &c->st->abort;
     a.host_abort = c->host_abort_dev;
+    a.step_epoch = advance_step ? &c->st->step_epoch : nullptr;
     a.rank = p.rank;
     a.world = p.world;
-    a.advance_step = advance_step ? 1 : 0;
-    ctx_barrier_kernel<<<1, 32, 0, st>>>(a);
+    peer_barrier_epoch_kernel<<<1, 32, 0, st>>>(a);
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -408,6 +371,17 @@ int enqueue_step_pipelined(b200ps_ctx* c, cudaStream_t st) {
     return barrier(c, st, true);
 }
 
+// experiment knob (B200PS_STEP_EVENTS = 1 | 2): an event record behind every phase of the sequential step
+void phase_event(b200ps_ctx* c, cudaStream_t st, int k) {
+    static const int mode = getenv("B200PS_STEP_EVENTS") ? atoi(getenv("B200PS_STEP_EVENTS")) : 0;
+    if (!mode || c->profile) return;
+    if (c->phase_ev.size() < 4) {
+        c->phase_ev.resize(4, nullptr);
+        for (auto& e : c->phase_ev) cudaEventCreateWithFlags(&e, mode == 2 ? cudaEventDefault : cudaEventDisableTiming);
+    }
+    cudaEventRecord(c->phase_ev[(size_t)k], st);
+}
+
 int enqueue_step(b200ps_ctx* c, cudaStream_t st) {
     const auto& p = *c->plan;
     if (c->pipelined && !c->profile) return enqueue_step_pipelined(c, st);
@@ -415,13 +389,18 @@ int enqueue_step(b200ps_ctx* c, cudaStream_t st) {
         Mark m(c, 0, st);
         if (int rc = launch_fold(c, 0, p.P, st)) return rc;
     }
+    phase_event(c, st, 0);
     if (int rc = barrier(c, st)) return rc;  // every worker's gradient (or every GPU's partial sum) is in place
+    phase_event(c, st, 1);
     {
         Mark m(c, 1, st);
         for (size_t i = 0; i < p.launches.size(); ++i)
             if (int rc = launch_apply(c, i, p.launches[i].begin, p.launches[i].end, c->t + 1, st)) return rc;
     }
-    return barrier(c, st);  // every replica holds every updated slice
+    phase_event(c, st, 2);
+    const int rc = barrier(c, st);  // every replica holds every updated slice
+    phase_event(c, st, 3);
+    return rc;
 }
 
 int zero_state(b200ps_ctx* c, cudaStream_t st) {

@@ -398,6 +398,7 @@ int max_threads_for(Kern kern) {
 
 // kernel function -> OPT_*, filled as instantiations are first launched: lets a context find the
 // apply nodes of a captured graph (dense_node_opt) and re-arm their step size (dense_node_set_lr)
+constexpr int MC_NODE = 0x100;  // the node's argument is a McApply, not a DenseParams
 std::mutex g_registry_mutex;
 std::map<const void*, int> g_registry;
 
@@ -522,6 +523,12 @@ int dense_launch_mc(const McApply& a, int ctas_per_sm, cudaStream_t stream) {
     const uint64_t want = (a.n / 4 + 511) / 512, cap = (uint64_t)sms * (uint64_t)ctas_per_sm;
     const int grid = (int)(want < cap ? want : cap);
     cudaStream_t st = stream;
+    static const bool registered = [] {  // graph replay re-arms the step size of these nodes too (dense_node_set_lr)
+        std::lock_guard<std::mutex> lock(g_registry_mutex);
+        g_registry[(const void*)dense_apply_mc_kernel<OPT_ADAM>] = OPT_ADAM | MC_NODE;
+        return true;
+    }();
+    (void)registered;
     switch (a.opt) {
         case OPT_ADAM: dense_apply_mc_kernel<OPT_ADAM><<<grid, 256, 0, st>>>(a); break;
         case OPT_MOMENTUM: dense_apply_mc_kernel<OPT_MOMENTUM><<<grid, 256, 0, st>>>(a); break;
@@ -552,16 +559,31 @@ int dense_node_opt(cudaGraphNode_t node) {
     if (cudaGraphKernelNodeGetParams(node, &kp) != cudaSuccess) return -1;
     std::lock_guard<std::mutex> lock(g_registry_mutex);
     auto it = g_registry.find(kp.func);
-    return it == g_registry.end() ? -1 : it->second;
+    return it == g_registry.end() ? -1 : (it->second & 0xff);
 }
 
 cudaError_t dense_node_set_lr(cudaGraphExec_t exec, cudaGraphNode_t node, float lr) {
     cudaKernelNodeParams kp{};
     cudaError_t e = cudaGraphKernelNodeGetParams(node, &kp);
     if (e != cudaSuccess) return e;
-    DenseParams a = *static_cast<const DenseParams*>(kp.kernelParams[0]);  // the node's copy of the launch arguments
-    a.lr = lr;
-    void* args[1] = {&a};
+    bool mc = false;
+    {
+        std::lock_guard<std::mutex> lock(g_registry_mutex);
+        auto it = g_registry.find(kp.func);
+        mc = it != g_registry.end() && (it->second & MC_NODE);
+    }
+    DenseParams a{};
+    McApply b{};
+    void* args[1];
+    if (mc) {
+        b = *static_cast<const McApply*>(kp.kernelParams[0]);  // the node's copy of the launch arguments
+        b.lr = lr;
+        args[0] = &b;
+    } else {
+        a = *static_cast<const DenseParams*>(kp.kernelParams[0]);
+        a.lr = lr;
+        args[0] = &a;
+    }
     kp.kernelParams = args;
     return cudaGraphExecKernelNodeSetParams(exec, node, &kp);
 }

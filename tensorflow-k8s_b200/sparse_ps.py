@@ -1,21 +1,14 @@
-"""Host side of the sparse PS path for the tasks on THIS GPU.
+"""Host mirror of the table group of include/b200ps.h: `EmbeddingTable` is a thin ctypes wrapper of
+one `b200ps_table_t` (csrc/table.cu) -- the shards of an embedding table and the buffers of the
+compute tasks that live on THIS process's GPU.
 
-An embedding table of `rows` x `dim` fp32 is partitioned by TF "div" over S PS shards; shard s
-lives on GPU s mod G, compute task w on GPU w mod G.  Each rank keeps one exported arena:
-
-    [ rows of local shard 0 | local shard 1 | ... | (Adagrad accumulators, same order) |
-      per local worker: ids int64[B] | gradient rows fp32[B, dim] | pulled rows fp32[B, dim] |
-      per REMOTE worker: staging fp32[B, dim] for the gradient rows it routes here ]
-
-Every rank can compute every other rank's layout, so after the one-time handle exchange a kernel
-is given plain base pointers, and the routing all-to-alls of a classic PS are fused into kernels:
-ids are streamed from wherever the workers wrote them, and rows cross NVLink only as posted
-stores -- `pull_step`: each owner serves the rows of its shards into the requesting workers'
-buffers; `push_step`: each worker's GPU routes the rows other GPUs own into their staging slots,
-then every GPU sorts the ids of ITS shards and folds rows out of local memory only.
+The arena layout, the CUDA-IPC mapping of the other ranks' arenas, the pointer tables the kernels
+take, the peer-memory barriers, the pull / push sequences, graph replay and checkpoints live behind
+the C ABI.  Here: torch tensor views of the library's device memory and `torch.distributed` to move
+the 64-byte handles between the ranks (one process per GPU).
 
 Reference: none (TensorFlow's embedding_lookup / sparse apply ops inside the containers a TFJob
-launches); roles per k8s-operator.md:6.  torch is plumbing (streams, distributed rendezvous).
+launches); roles per k8s-operator.md:6.
 """
 from __future__ import annotations
 
@@ -25,25 +18,18 @@ from typing import Dict, List, Optional, Tuple
 import numpy as np
 import torch
 
-from ._lib import TableGeom, check, lib
-from .contract import placement_gpu
+from . import _lib
+from ._lib import TableOptions, check, lib
+from .contract import Cluster, placement_gpu
 from .layout import row_range
 
 IPC_BYTES = 64
-BARRIER_WORDS = 16  # B200PS_BARRIER_WORDS
-
-
-def _up(x: int, a: int = 256) -> int:
-    return (x + a - 1) // a * a
-
-
-class _ByteArray:
-    def __init__(self, ptr: int, nbytes: int, typestr: str, shape):
-        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+_NONE = (1 << 64) - 1
 
 
 class TableLayout:
-    """Pure arithmetic: where everything lives, for every rank (testable without a GPU)."""
+    """Where everything lives, for every rank: the library's arithmetic (b200ps_table_layout), readable
+    without a GPU."""
 
     def __init__(self, rows: int, dim: int, S: int, W: int, B: int, world: int, adagrad: bool):
         self.rows, self.dim, self.S, self.W, self.B, self.world, self.adagrad = rows, dim, S, W, B, world, adagrad
@@ -57,28 +43,25 @@ class TableLayout:
         self.flag_off: Dict[int, int] = {}
         self.arena_bytes: List[int] = []
         for r in range(world):
-            off = 0
-            mine = [s for s in range(S) if placement_gpu(s, world) == r]
-            for s in mine:
-                self.shard_off[s] = off
-                off += _up((self.shard_range[s][1] - self.shard_range[s][0]) * dim * 4)
-            if adagrad:
-                for s in mine:
-                    self.accum_off[s] = off
-                    off += _up((self.shard_range[s][1] - self.shard_range[s][0]) * dim * 4)
-            for w in (w for w in range(W) if placement_gpu(w, world) == r):
-                self.ids_off[w] = off
-                off += _up(B * 8)
-                self.grad_off[w] = off
-                off += _up(B * dim * 4)
-                self.out_off[w] = off
-                off += _up(B * dim * 4)
-            for w in (w for w in range(W) if placement_gpu(w, world) != r):
-                self.stage_off[(r, w)] = off  # rows worker w routes to GPU r
-                off += _up(B * dim * 4)
-            self.flag_off[r] = off  # barrier flags behind everything else
-            off += _up(BARRIER_WORDS * 4)
-            self.arena_bytes.append(off)
+            ab, fo = C.c_uint64(), C.c_uint64()
+            so, ao = (C.c_uint64 * S)(), (C.c_uint64 * S)()
+            io, go, oo, st = (C.c_uint64 * W)(), (C.c_uint64 * W)(), (C.c_uint64 * W)(), (C.c_uint64 * W)()
+            rc = lib.b200ps_table_layout(rows, dim, S, W, B, world, int(adagrad), r, C.byref(ab), C.byref(fo), so, ao, io, go, oo, st)
+            if rc == _lib.ERR_RANGE:
+                raise ValueError(_lib.last_error())
+            check(rc)
+            self.arena_bytes.append(ab.value)
+            self.flag_off[r] = fo.value
+            for s in range(S):
+                if so[s] != _NONE:
+                    self.shard_off[s] = so[s]
+                if ao[s] != _NONE:
+                    self.accum_off[s] = ao[s]
+            for w in range(W):
+                if io[w] != _NONE:
+                    self.ids_off[w], self.grad_off[w], self.out_off[w] = io[w], go[w], oo[w]
+                if st[w] != _NONE:
+                    self.stage_off[(r, w)] = st[w]  # rows worker w routes to GPU r
 
     def shard_rank(self, s: int) -> int:
         return placement_gpu(s, self.world)
@@ -87,24 +70,41 @@ class TableLayout:
         return placement_gpu(w, self.world)
 
 
+class _DevArray:
+    def __init__(self, ptr: int, typestr: str, shape):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class _Replay:
+    def __init__(self, tab):
+        self._tab = tab
+
+    def replay(self):
+        self._tab.step()
+
+
 class EmbeddingTable:
     def __init__(self, rows: int, dim: int, num_shards: int, num_workers: int, ids_per_worker: int,
                  optimizer: str = "sgd", lr: float = 0.05, rank: int = 0, world: int = 1, group=None,
-                 accum_init: float = 0.1, barrier: str = "nccl"):
-        if barrier not in ("peer", "nccl"):
-            raise ValueError("barrier must be 'peer' or 'nccl'")
+                 accum_init: float = 0.1, use_graph: bool = False, cluster: Optional[Cluster] = None):
         if optimizer not in ("sgd", "adagrad"):
             raise ValueError("optimizer must be 'sgd' or 'adagrad'")
         if not torch.cuda.is_available():
             raise RuntimeError("b200ps.EmbeddingTable needs a CUDA device: there is no CPU fallback")
+        from .ps import synthetic_cluster
+
+        self.cluster = cluster if cluster is not None else synthetic_cluster(num_shards, num_workers)
+        if (self.cluster.num_shards, self.cluster.num_workers) != (num_shards, num_workers):
+            raise ValueError("the cluster's ps / compute task counts differ from num_shards / num_workers")
         self.lay = TableLayout(rows, dim, num_shards, num_workers, ids_per_worker, world, optimizer == "adagrad")
         self.optimizer, self.lr, self.rank, self.world, self.group = optimizer, lr, rank, world, group
-        self.geom = TableGeom(rows, dim, num_shards, rank, world)
-        nbytes = self.lay.arena_bytes[rank]
-        p = C.c_void_p()
-        check(lib.b200ps_dev_alloc(nbytes, C.byref(p)))
-        self.base: Dict[int, int] = {rank: p.value}
-        self._own = p.value
+        o = TableOptions()
+        check(lib.b200ps_table_options_default(C.byref(o)))
+        o.optimizer = _lib.OPT_ADAGRAD if optimizer == "adagrad" else _lib.OPT_SGD
+        o.lr, o.accum_init, o.use_graph = lr, accum_init, int(use_graph)
+        h = C.c_void_p()
+        check(lib.b200ps_table_create(self.cluster._h, rows, dim, ids_per_worker, rank, world, C.byref(o), C.byref(h)))
+        self._h = h
         self.local_shards = [s for s in range(num_shards) if self.lay.shard_rank(s) == rank]
         self.local_workers = [w for w in range(num_workers) if self.lay.worker_rank(w) == rank]
         dev = torch.device("cuda", torch.cuda.current_device())
@@ -112,164 +112,123 @@ class EmbeddingTable:
         self.shards: Dict[int, torch.Tensor] = {}
         self.accums: Dict[int, torch.Tensor] = {}
         for s in self.local_shards:
-            n = self.lay.shard_range[s][1] - self.lay.shard_range[s][0]
-            self.shards[s] = torch.as_tensor(_ByteArray(p.value + self.lay.shard_off[s], n * dim * 4, "<f4", (n, dim)), device=dev)
-            if self.lay.adagrad:
-                self.accums[s] = torch.as_tensor(_ByteArray(p.value + self.lay.accum_off[s], n * dim * 4, "<f4", (n, dim)), device=dev)
-                self.accums[s].fill_(accum_init)
+            p, a, b, e = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint64()
+            check(lib.b200ps_table_shard(h, s, C.byref(p), C.byref(a), C.byref(b), C.byref(e)))
+            n = e.value - b.value
+            self.shards[s] = torch.as_tensor(_DevArray(p.value, "<f4", (max(n, 1), dim)), device=dev)[:n]
+            if a.value:
+                self.accums[s] = torch.as_tensor(_DevArray(a.value, "<f4", (max(n, 1), dim)), device=dev)[:n]
         self.ids: Dict[int, torch.Tensor] = {}
         self.grad_rows: Dict[int, torch.Tensor] = {}
         self.pulled: Dict[int, torch.Tensor] = {}
         for w in self.local_workers:
-            self.ids[w] = torch.as_tensor(_ByteArray(p.value + self.lay.ids_off[w], B * 8, "<i8", (B,)), device=dev)
-            self.grad_rows[w] = torch.as_tensor(_ByteArray(p.value + self.lay.grad_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
-            self.pulled[w] = torch.as_tensor(_ByteArray(p.value + self.lay.out_off[w], B * dim * 4, "<f4", (B, dim)), device=dev)
-        self.workspace = torch.empty(int(lib.b200ps_sparse_workspace_bytes(num_workers * B, dim)), dtype=torch.uint8, device=dev)
-        self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.barrier_kind, self._epoch = barrier, 0
-        torch.as_tensor(_ByteArray(p.value + self.lay.flag_off[rank], BARRIER_WORDS * 4, "<i4", (BARRIER_WORDS,)), device=dev).zero_()
+            i, g, p = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            check(lib.b200ps_table_worker_buffers(h, w, C.byref(i), C.byref(g), C.byref(p)))
+            self.ids[w] = torch.as_tensor(_DevArray(i.value, "<i8", (B,)), device=dev)
+            self.grad_rows[w] = torch.as_tensor(_DevArray(g.value, "<f4", (B, dim)), device=dev)
+            self.pulled[w] = torch.as_tensor(_DevArray(p.value, "<f4", (B, dim)), device=dev)
         if world > 1:
             self._exchange_handles()
-            self._flag_ptrs = (C.c_void_p * world)(*[self.base[r] + self.lay.flag_off[r] for r in range(world)])
-            import torch.distributed as dist
-
-            torch.cuda.synchronize()
-            dist.barrier(group=group)  # flags zeroed and arenas mapped everywhere
-        L = self.lay
-        self._shard_ptrs = (C.c_void_p * num_shards)(*[self.base[L.shard_rank(s)] + L.shard_off[s] for s in range(num_shards)])
-        self._accum_ptrs = (C.c_void_p * num_shards)(*[(self.base[L.shard_rank(s)] + L.accum_off[s]) if L.adagrad else 0
-                                                       for s in range(num_shards)])
-        self._ids_ptrs = (C.c_void_p * num_workers)(*[self.base[L.worker_rank(w)] + L.ids_off[w] for w in range(num_workers)])
-        # apply reads local memory only: a local worker's own buffer, or this GPU's staging slot for a remote one
-        self._grad_ptrs = (C.c_void_p * num_workers)(*[
-            self.base[rank] + (L.grad_off[w] if L.worker_rank(w) == rank else L.stage_off[(rank, w)]) for w in range(num_workers)])
-        self._out_ptrs = (C.c_void_p * num_workers)(*[self.base[L.worker_rank(w)] + L.out_off[w] for w in range(num_workers)])
-        self._route_dst = {w: (C.c_void_p * world)(*[0 if o == rank else self.base[o] + L.stage_off[(o, w)] for o in range(world)])
-                           for w in self.local_workers}
 
     def _exchange_handles(self):
         import torch.distributed as dist
 
-        buf = C.create_string_buffer(IPC_BYTES)
-        check(lib.b200ps_ipc_export(C.c_void_p(self._own), buf))
+        mine = C.create_string_buffer(IPC_BYTES)
+        check(lib.b200ps_table_export_handle(self._h, mine))
         blobs: List[Optional[bytes]] = [None] * self.world
-        dist.all_gather_object(blobs, buf.raw, group=self.group)
-        for r, blob in enumerate(blobs):
-            if r != self.rank:
-                q = C.c_void_p()
-                check(lib.b200ps_ipc_open(C.create_string_buffer(blob, IPC_BYTES), C.byref(q)))
-                self.base[r] = q.value
+        dist.all_gather_object(blobs, mine.raw, group=self.group)
+        check(lib.b200ps_table_import_handles(self._h, C.create_string_buffer(b"".join(blobs), IPC_BYTES * self.world)))
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)  # flags zeroed and arenas mapped everywhere
 
     def close(self):
+        if not getattr(self, "_h", None):
+            return
         torch.cuda.synchronize()
         if self.world > 1:
             import torch.distributed as dist
 
             dist.barrier(group=self.group)
-        for r, b in list(self.base.items()):
-            if r != self.rank:
-                lib.b200ps_ipc_close(C.c_void_p(b))
         self.shards, self.accums, self.ids, self.grad_rows, self.pulled = {}, {}, {}, {}, {}
-        if self._own:
-            check(lib.b200ps_dev_free(C.c_void_p(self._own)))
-            self._own = 0
+        h, self._h = self._h, None
+        check(lib.b200ps_table_destroy(h))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) and self.world == 1:
+                lib.b200ps_table_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
 
     @staticmethod
     def _stream() -> C.c_void_p:
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
-    def _barrier(self):
-        if self.world > 1:
-            if self.barrier_kind == "peer":
-                self._epoch += 1
-                check(lib.b200ps_peer_barrier(self._flag_ptrs, self.rank, self.world, self._epoch, self._stream()))
-            else:
-                import torch.distributed as dist
-
-                dist.all_reduce(self._flag, group=self.group)
-
     def check_barriers(self):
-        if self.world > 1 and self.barrier_kind == "peer":
-            check(lib.b200ps_peer_barrier_error(C.c_void_p(self._own + self.lay.flag_off[self.rank]), self._stream()))
+        check(lib.b200ps_table_sync(self._h, self._stream()))
 
     # ---- table -------------------------------------------------------------------------------
     def init_uniform(self, seed: int = 1):
         """table[i, d] = u(seed, 0, 0, i*dim + d) on the shards of this GPU."""
-        for s in self.local_shards:
-            b, _ = self.lay.shard_range[s]
-            t = self.shards[s]
-            check(lib.b200ps_fill_uniform(C.c_void_p(t.data_ptr()), t.numel(), seed, 0, 0, b * self.lay.dim, self._stream()))
+        check(lib.b200ps_table_init_uniform(self._h, seed, self._stream()))
 
     # ---- worker-facing -----------------------------------------------------------------------
     def pull(self, worker: int, out: torch.Tensor) -> torch.Tensor:
         """a10: out[k, :] = table[ids_w[k], :] for a local worker, rows read from the owning GPUs."""
-        check(lib.b200ps_sparse_gather(C.c_void_p(out.data_ptr()), self._shard_ptrs, C.byref(self.geom),
-                                       C.c_void_p(self.ids[worker].data_ptr()), self.lay.B, self._stream()))
+        check(lib.b200ps_sparse_pull_worker(self._h, worker, C.c_void_p(out.data_ptr()), self._stream()))
         return out
-
-    def serve(self):
-        """Owner side of pull for every worker: rows of this GPU's shards -> the workers' `pulled` buffers."""
-        check(lib.b200ps_sparse_serve(self._out_ptrs, self._shard_ptrs, self._ids_ptrs, self.lay.W, self.lay.B,
-                                      C.byref(self.geom), self._stream()))
 
     def pull_step(self):
         """a10 for all workers of the job at once (collective): afterwards `pulled[w]` holds
         table[ids_w] for every local worker w."""
-        self._barrier()  # every worker's ids are written
-        self.serve()
-        self._barrier()  # every owner has delivered its rows
-
-    def route(self):
-        """Worker side of push: gradient rows owned by other GPUs go to their staging slots."""
-        for w in self.local_workers:
-            check(lib.b200ps_sparse_route(C.c_void_p(self.grad_rows[w].data_ptr()), C.c_void_p(self.ids[w].data_ptr()),
-                                          self.lay.B, C.byref(self.geom), self._route_dst[w], self._stream()))
-
-    def sort_segment(self):
-        """a11: the plan (sorted ids, permutation, segments) of this GPU's shards, into the workspace."""
-        check(lib.b200ps_sparse_sort_segment(self._ids_ptrs, self.lay.W, self.lay.B, C.byref(self.geom),
-                                             C.c_void_p(self.workspace.data_ptr()), self.workspace.numel(), self._stream()))
-
-    def apply(self):
-        """a12: fold the gradient rows of every unique id of the plan and update its row."""
-        if self.optimizer == "sgd":
-            check(lib.b200ps_sparse_apply_sgd(self._shard_ptrs, self._grad_ptrs, self.lay.W, self.lay.B, C.byref(self.geom),
-                                              self.lr, C.c_void_p(self.workspace.data_ptr()), self._stream()))
-        else:
-            check(lib.b200ps_sparse_apply_adagrad(self._shard_ptrs, self._accum_ptrs, self._grad_ptrs, self.lay.W, self.lay.B,
-                                                  C.byref(self.geom), self.lr, C.c_void_p(self.workspace.data_ptr()),
-                                                  self._stream()))
+        check(lib.b200ps_sparse_pull(self._h, self._stream()))
 
     def push_step(self):
         """a11 + a12 for the shards of this GPU over every worker's (ids, gradient rows)."""
-        if self.world > 1:
-            self.route()
-        self._barrier()  # all workers' ids are written and every routed row has landed
-        self.sort_segment()
-        self.apply()
-        self._barrier()  # every shard is updated before anyone pulls again
+        check(lib.b200ps_sparse_push(self._h, self._stream()))
 
-    def capture_step(self) -> "torch.cuda.CUDAGraph":
-        """pull_step + push_step of one GPU as a CUDA graph: ~25 small launches (radix passes, scans,
-        segments) replayed without per-launch host work.  All counts live on the device and every
-        grid is fixed, so the graph is valid for any ids / gradient rows written into the same
-        buffers.  One GPU only (the cross-rank barriers are not captured)."""
-        if self.world != 1:
-            raise ValueError("capture_step supports one GPU")
-        self.pull_step()
-        self.push_step()
-        torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.pull_step()
-            self.push_step()
-        return g
+    def step(self):
+        """pull of every worker + push, sharing one barrier (what a training step does)."""
+        check(lib.b200ps_sparse_step(self._h, self._stream()))
+
+    def capture_step(self) -> _Replay:
+        """Switches `step` to CUDA-graph replay (~25 small launches -- radix passes, scans, segments --
+        replayed without per-launch host work; all counts live on the device and every grid is fixed,
+        so the graph is valid for any ids / gradient rows written into the same buffers) and runs one
+        step, which captures it.  Works across ranks too: the barriers' epoch lives in device memory."""
+        check(lib.b200ps_table_set_graph(self._h, 1))
+        self.step()
+        return _Replay(self)
+
+    @property
+    def profile(self) -> bool:
+        return getattr(self, "_profile", False)
+
+    @profile.setter
+    def profile(self, on: bool):
+        self._profile = bool(on)
+        check(lib.b200ps_table_set_profile(self._h, int(self._profile)))
+
+    def phase_ms(self) -> Dict[str, float]:
+        a, b, c = C.c_float(), C.c_float(), C.c_float()
+        check(lib.b200ps_table_phase_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"serve_pull": a.value, "route+barrier+sort_segment": b.value, "apply": c.value}
 
     def plan(self) -> dict:
-        """The plan of the last sort_segment as NumPy arrays (debug accessor; synchronises)."""
-        from .kernels import sparse_plan_read
-
-        return sparse_plan_read(self.workspace, self.lay.W * self.lay.B, self.lay.rows)
+        """The plan of the last push as NumPy arrays (debug accessor; synchronises)."""
+        n_total = self.lay.W * self.lay.B
+        kept, uniq, bad = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        s = np.empty(n_total, np.int64)
+        perm = np.empty(n_total, np.uint32)
+        seg = np.empty(n_total, np.int32)
+        un = np.empty(n_total, np.int64)
+        off = np.empty(n_total + 1, np.uint32)
+        check(lib.b200ps_table_plan_read(self._h, C.byref(kept), C.byref(uniq), C.byref(bad), s.ctypes.data, perm.ctypes.data,
+                                         seg.ctypes.data, un.ctypes.data, off.ctypes.data, self._stream()))
+        k, u = kept.value, uniq.value
+        return {"n_kept": k, "n_unique": u, "n_bad": bad.value, "sorted_ids": s[:k], "perm": perm[:k], "seg_id": seg[:k],
+                "unique_ids": un[:u], "seg_offset": off[:u + 1]}
 
     def dump(self) -> Dict[int, Tuple[Tuple[int, int], np.ndarray]]:
         self.check_barriers()
@@ -278,38 +237,21 @@ class EmbeddingTable:
 
     # ---- checkpoint / resume of the table shards ---------------------------
     def save(self, directory: str):
-        """Every rank writes its shards (and Adagrad accumulators) with the row partition as header:
-        <directory>/table-rank<r>-of-<G>.npz."""
-        import json
-        import os
+        """Every rank writes its shards (and Adagrad accumulators) with the geometry as header:
+        <directory>/table-rank<r>-of-<G>.b200ps (temporary file + rename)."""
+        check(lib.b200ps_table_save(self._h, directory.encode(), self._stream()))
+        if self.world > 1:
+            import torch.distributed as dist
 
-        os.makedirs(directory, exist_ok=True)
-        self.check_barriers()
-        torch.cuda.synchronize()
-        L = self.lay
-        header = {"format": "b200ps-table-1", "rows": L.rows, "dim": L.dim, "shards": L.S, "optimizer": self.optimizer,
-                  "rank": self.rank, "world": self.world, "ranges": {str(s): list(L.shard_range[s]) for s in self.local_shards}}
-        arrays = {"header": np.frombuffer(json.dumps(header).encode(), dtype=np.uint8)}
-        for s in self.local_shards:
-            arrays[f"rows{s}"] = self.shards[s].cpu().numpy()
-            if L.adagrad:
-                arrays[f"accum{s}"] = self.accums[s].cpu().numpy()
-        np.savez(os.path.join(directory, f"table-rank{self.rank}-of-{self.world}.npz"), **arrays)
+            dist.barrier(group=self.group)
 
     def load(self, directory: str):
         """Restores this rank's shards from a checkpoint written with the same geometry and world size."""
-        import json
-        import os
-
-        z = np.load(os.path.join(directory, f"table-rank{self.rank}-of-{self.world}.npz"))
-        h = json.loads(bytes(z["header"]).decode())
-        L = self.lay
-        if (h["rows"], h["dim"], h["shards"], h["optimizer"], h["world"]) != (L.rows, L.dim, L.S, self.optimizer, self.world):
-            raise ValueError(f"table checkpoint was written for a different geometry: {h}")
-        for s in self.local_shards:
-            self.shards[s].copy_(torch.from_numpy(z[f"rows{s}"]))
-            if L.adagrad:
-                self.accums[s].copy_(torch.from_numpy(z[f"accum{s}"]))
+        rc = lib.b200ps_table_load(self._h, directory.encode(), self._stream())
+        if rc == _lib.ERR_INVALID:
+            msg = _lib.last_error()
+            raise (FileNotFoundError if "cannot read" in msg else ValueError)(msg)
+        check(rc)
         torch.cuda.synchronize()
 
     def bytes_per_step(self, n_unique_local: int) -> Dict[str, int]:

@@ -31,12 +31,21 @@ def main():
         for w in tab.local_workers:
             tab.ids[w].copy_(torch.from_numpy(ids[w]))
             tab.grad_rows[w].copy_(torch.from_numpy(grad[w]))
-        tab.pull_step()  # owners serve rows into the workers' buffers (posted NVLink stores)
+        if step == 1:
+            tab.pull_step()  # owners serve rows into the workers' buffers (posted NVLink stores)
+            for w in tab.local_workers:
+                tab.pull(w, out)  # the single-worker form reads peer shards directly
+                ok = ok and np.array_equal(out.cpu().numpy().view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
+            pulled = {w: tab.pulled[w].cpu().numpy() for w in tab.local_workers}
+            tab.push_step()
+        elif step == 2:
+            tab.step()  # pull + push sharing one barrier (b200ps_sparse_step)
+            pulled = {w: tab.pulled[w].cpu().numpy() for w in tab.local_workers}
+        else:
+            tab.capture_step()  # the same, captured and replayed as one CUDA graph per rank (barriers included)
+            pulled = {w: tab.pulled[w].cpu().numpy() for w in tab.local_workers}
         for w in tab.local_workers:
-            ok = ok and np.array_equal(tab.pulled[w].cpu().numpy().view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
-            tab.pull(w, out)  # the single-worker form reads peer shards directly
-            ok = ok and np.array_equal(out.cpu().numpy().view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
-        tab.push_step()
+            ok = ok and np.array_equal(pulled[w].view(np.uint32), O.gather(table, ids[w]).view(np.uint32))
         inv_w = np.float32(1.0) / np.float32(W)
         if opt == "sgd":
             O.sparse_apply_sgd(table, 0, grad.reshape(-1, dim), ids.reshape(-1), inv_w, np.float32(0.05))

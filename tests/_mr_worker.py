@@ -18,12 +18,13 @@ def main():
     S, W, opt, transport, steps = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3], sys.argv[4], 3
     aggregate = sys.argv[5] if len(sys.argv) > 5 else "flat"
     overlap = (sys.argv[6] == "overlap") if len(sys.argv) > 6 else False
+    graph = (sys.argv[7] == "graph") if len(sys.argv) > 7 else False
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sizes = [700_000, 333, 123_456, 2_000_000]
     ps = b200ps.ParameterServer(sizes, S, W, optimizer=opt, lr=1e-3 if opt == "adam" else 0.05, rank=rank, world=world,
-                                transport=transport, aggregate=aggregate, overlap=overlap)
+                                transport=transport, aggregate=aggregate, overlap=overlap, use_graph=graph)
     ps.init_uniform(1)
     P = ps.plan.P
     hp = O.fill_uniform(P, 1, 0, 0, threads=4)

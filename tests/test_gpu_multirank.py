@@ -99,3 +99,19 @@ def test_in_switch_reduction_matches_within_tolerance(S, W, opt, mode):
     if not b200ps._lib.lib.b200ps_multicast_supported():
         pytest.skip("the device reports no multicast support")
     _run(2, S, W, opt, "peer", "multimem", mode)
+
+
+@pytest.mark.parametrize("aggregate,mode", [("two_level", "sequential"), ("two_level", "overlap"), ("multimem", "overlap")])
+def test_whole_rank_step_replayed_as_one_cuda_graph(aggregate, mode):
+    """fold -> barrier -> applies -> barrier (or the pipelined form) of every rank captured once and replayed:
+    the barrier epoch lives in device memory and Adam's step size is re-armed on the apply nodes."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    if aggregate == "multimem":
+        import b200ps
+
+        torch.cuda.set_device(0)
+        if not b200ps._lib.lib.b200ps_multicast_supported():
+            pytest.skip("the device reports no multicast support")
+    _run(2, 4, 8, "adam", "peer", aggregate, mode, "graph")
