@@ -132,7 +132,9 @@ struct Smem {
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + tmem pointer, + slack for 1024-byte alignment
+    static constexpr int STAGING_OFFSET = BAR_OFFSET + 256;          // EPI_WGRAD: 4 warps x 32 rows x 36 floats
+    static constexpr int STAGING_BYTES = 4 * 32 * 36 * 4;
+    static constexpr int TOTAL = STAGING_OFFSET + STAGING_BYTES + 1024;  // + slack for 1024-byte alignment
 };
 
 template <int BN, int EPI>
@@ -240,13 +242,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                 tmem_ld32(t_row + (uint32_t)(c * 32), v);
                 const int n0 = n_blk * BN + c * 32;
                 if (EPI == EPI_WGRAD) {
-                    float* dst = g.out32[z] + (size_t)m * g.N + n0;
+                    // fp32 rows straight into the task's gradient buffer.  A thread holds one ROW of the tile, so
+                    // storing from registers would touch 32 different rows per instruction (16-byte pieces); the
+                    // 32 x 32 block is turned through a per-warp shared-memory tile instead (conflict-free both
+                    // ways with a 36-float pitch) and leaves as full 128-byte lines, four rows per instruction.
+                    float* stg = reinterpret_cast<float*>(smem + S::STAGING_OFFSET) + lane_grp * (32 * 36);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        float4 o = make_float4(__uint_as_float(v[j]) * g.scale, __uint_as_float(v[j + 1]) * g.scale,
-                                               __uint_as_float(v[j + 2]) * g.scale, __uint_as_float(v[j + 3]) * g.scale);
-                        *reinterpret_cast<float4*>(dst + j) = o;
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<float4*>(stg + lane * 36 + j) =
+                            make_float4(__uint_as_float(v[j]) * g.scale, __uint_as_float(v[j + 1]) * g.scale,
+                                        __uint_as_float(v[j + 2]) * g.scale, __uint_as_float(v[j + 3]) * g.scale);
+                    __syncwarp();
+                    float* dst = g.out32[z] + (size_t)(m_blk * BM + lane_grp * 32) * g.N + n0;
+                    const int sub = lane >> 3, col = (lane & 7) * 4;
+#pragma unroll
+                    for (int r4 = 0; r4 < 32; r4 += 4) {
+                        const float4 o = *reinterpret_cast<const float4*>(stg + (r4 + sub) * 36 + col);
+                        *reinterpret_cast<float4*>(dst + (size_t)(r4 + sub) * g.N + col) = o;
                     }
+                    __syncwarp();
                 } else {
                     __align__(16) __nv_bfloat16 h[32];
                     if (EPI == EPI_FWD) {

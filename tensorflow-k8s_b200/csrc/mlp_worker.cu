@@ -199,6 +199,8 @@ struct b200ps_mlp {
     std::vector<CUtensorMap> f_a, f_b, d_a, d_b, g_a, g_b;
     std::vector<int> f_bn, d_bn, g_bn;   // N tile per GEMM (256, or 128 when N is not a multiple of 256)
     std::vector<void*> owned;
+    cudaStream_t s_copy = nullptr;       // the targets travel beside the forward pass
+    cudaEvent_t ev_start = nullptr, ev_targets = nullptr;
 };
 
 namespace {
@@ -291,12 +293,19 @@ extern "C" int b200ps_mlp_create(const int* dims, int n_dims, int batch_per_task
         if (int rc = make_map(&m->g_a[l], m->actT[l], in, M, gemm::BM)) return rc;
         if (int rc = make_map(&m->g_b[l], m->dactT[l + 1], on, M, m->g_bn[l])) return rc;
     }
+    B200PS_CUDA(cudaStreamCreateWithFlags(&m->s_copy, cudaStreamNonBlocking));
+    B200PS_CUDA(cudaEventCreateWithFlags(&m->ev_start, cudaEventDisableTiming));
+    B200PS_CUDA(cudaEventCreateWithFlags(&m->ev_targets, cudaEventDisableTiming));
     *out = m.release();
     return B200PS_OK;
 }
 
 extern "C" int b200ps_mlp_destroy(b200ps_mlp_t* m) {
     if (!m) return B200PS_OK;
+    cudaDeviceSynchronize();
+    if (m->s_copy) cudaStreamDestroy(m->s_copy);
+    if (m->ev_start) cudaEventDestroy(m->ev_start);
+    if (m->ev_targets) cudaEventDestroy(m->ev_targets);
     for (void* p : m->owned) cudaFree(p);
     delete m;
     return B200PS_OK;
@@ -309,8 +318,12 @@ extern "C" int b200ps_mlp_step(b200ps_mlp_t* m, const float* d_params, float* co
     const int L = m->L, M = m->M;
     const std::vector<int>& d = m->dims;
     // the step's host inputs: the mini-batches of the local tasks (features and targets), H2D
+    // (the targets are not needed before the loss: they are copied on a side stream while the forward pass runs)
+    B200PS_CUDA(cudaEventRecord(m->ev_start, st));  // behind the previous step's loss kernel, which read `target`
+    B200PS_CUDA(cudaStreamWaitEvent(m->s_copy, m->ev_start, 0));
+    B200PS_CUDA(cudaMemcpyAsync(m->target, h_t, (size_t)M * d[L] * sizeof(bf16), cudaMemcpyHostToDevice, m->s_copy));
+    B200PS_CUDA(cudaEventRecord(m->ev_targets, m->s_copy));
     B200PS_CUDA(cudaMemcpyAsync(m->act[0], h_x, (size_t)M * d[0] * sizeof(bf16), cudaMemcpyHostToDevice, st));
-    B200PS_CUDA(cudaMemcpyAsync(m->target, h_t, (size_t)M * d[L] * sizeof(bf16), cudaMemcpyHostToDevice, st));
     bool same = true;
     for (int w = 0; w < m->tasks; ++w) same = same && m->h_grad_ptrs[w] == d_grads[w];
     if (!same) {  // (a pageable source makes this copy synchronous: only when the buffers change)
@@ -338,6 +351,7 @@ extern "C" int b200ps_mlp_step(b200ps_mlp_t* m, const float* d_params, float* co
         if (int rc = run_gemm<gemm::EPI_FWD>(m->f_bn[l], m->f_a[l], m->f_b[l], g, m->sms, st)) return rc;
     }
     // loss and its gradient
+    B200PS_CUDA(cudaStreamWaitEvent(st, m->ev_targets, 0));
     loss_grad_kernel<<<dim3(d[L] / 32, M / 32), tb, 0, st>>>(m->act[L], m->target, m->dact[L], m->dactT[L], m->partial, M, d[L], m->batch);
     loss_final_kernel<<<m->tasks, 256, 0, st>>>(m->partial, m->loss, (m->batch / 32) * (d[L] / 32), m->batch);
     B200PS_CUDA(cudaGetLastError());
