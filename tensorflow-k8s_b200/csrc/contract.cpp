@@ -120,10 +120,14 @@ class JParser {
                 case 'u': {
                     unsigned cp, lo;
                     if (!hex4(cp)) return false;
-                    if (cp >= 0xD800 && cp < 0xDC00 && p_[0] == '\\' && p_[1] == 'u') {
+                    if (cp >= 0xD800 && cp < 0xDC00) {  // a high surrogate must be followed by \uDC00..\uDFFF
+                        if (!(p_[0] == '\\' && p_[1] == 'u')) return bad("lone surrogate in \\u escape");
                         p_ += 2;
                         if (!hex4(lo)) return false;
+                        if (lo < 0xDC00 || lo > 0xDFFF) return bad("mismatched surrogate pair in \\u escape");
                         cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+                    } else if (cp >= 0xDC00 && cp <= 0xDFFF) {
+                        return bad("lone surrogate in \\u escape");
                     }
                     utf8(s, cp);
                     break;
@@ -180,12 +184,33 @@ class JParser {
             case 'f': v.kind = JValue::Bool; v.b = false; return lit("false");
             case 'n': v.kind = JValue::Null; return lit("null");
             default: {
+                // the JSON number grammar first (strtod alone would also take 0x10, inf, nan, a leading '+'):
+                //   -? (0 | [1-9][0-9]*) (. [0-9]+)? ([eE] [+-]? [0-9]+)?
+                const char* q = p_;
+                if (*q == '-') ++q;
+                if (*q == '0') {
+                    ++q;
+                } else if (*q >= '1' && *q <= '9') {
+                    while (isdigit((unsigned char)*q)) ++q;
+                } else {
+                    return bad(p_ == q ? "unexpected character" : "bad number");
+                }
+                if (*q == '.') {
+                    ++q;
+                    if (!isdigit((unsigned char)*q)) return bad("bad number");
+                    while (isdigit((unsigned char)*q)) ++q;
+                }
+                if (*q == 'e' || *q == 'E') {
+                    ++q;
+                    if (*q == '+' || *q == '-') ++q;
+                    if (!isdigit((unsigned char)*q)) return bad("bad number");
+                    while (isdigit((unsigned char)*q)) ++q;
+                }
                 char* end = nullptr;
-                if (!(*p_ == '-' || isdigit((unsigned char)*p_))) return bad("unexpected character");
                 v.kind = JValue::Number;
                 v.num = strtod(p_, &end);
-                if (end == p_) return bad("bad number");
-                p_ = end;
+                if (end != q) return bad("bad number");
+                p_ = q;
                 return true;
             }
         }
@@ -224,8 +249,9 @@ std::string lower(std::string s) {
 
 bool is_int(const JValue& v, long lo, long hi, long& out) {
     if (v.kind != JValue::Number) return false;
+    if (!(v.num >= (double)lo && v.num <= (double)hi)) return false;  // also rejects inf / nan before the cast (UB otherwise)
     long x = (long)v.num;
-    if ((double)x != v.num || x < lo || x > hi) return false;
+    if ((double)x != v.num) return false;
     out = x;
     return true;
 }

@@ -42,7 +42,10 @@ constexpr int SCAN_TILE = SCAN_THREADS * 4;
 constexpr uint32_t SEG_CHUNK = 256;  // == PS_SEG_CHUNK of the oracle
 constexpr uint32_t NONE = 0xFFFFFFFFu;
 
-enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_NLONG = 4, HDR_NCHUNKS = 5, HDR_WORDS = 64 };
+enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_NLONG = 4, HDR_NCHUNKS = 5,
+       HDR_TAG = 8,       // identity of the plan (entries, geometry): written by sort_segment, checked by apply
+       HDR_MISMATCH = 9,  // raised by an apply that was given another push's workspace
+       HDR_WORDS = 64 };
 
 // Unsigned 32-bit division by a run-time constant without a divide instruction (Granlund &
 // Montgomery): exact for every 32-bit numerator.  A hardware-free u64 divide costs ~100
@@ -132,6 +135,17 @@ struct Workspace {
 };
 
 size_t align_up(size_t x) { return (x + 255) / 256 * 256; }
+
+// what identifies a plan: the push it was made for (never 0)
+uint32_t plan_tag(uint64_t n_total, uint64_t per_worker, const b200ps_table_geom_t* g) {
+    uint64_t z = n_total * 0x9E3779B97F4A7C15ull ^ per_worker * 0xBF58476D1CE4E5B9ull ^ g->rows * 0x94D049BB133111EBull ^
+                 ((uint64_t)g->nshards << 40) ^ ((uint64_t)g->rank << 20) ^ (uint64_t)g->world;
+    z ^= z >> 31;
+    z *= 0xD6E8FEB86659FD93ull;
+    z ^= z >> 29;
+    const uint32_t t = (uint32_t)z;
+    return t ? t : 1u;
+}
 
 // dim == 0: the part sort_segment and plan_read use (its offsets do not depend on dim)
 Workspace carve(void* base, uint64_t n, int dim) {
@@ -382,7 +396,7 @@ __global__ void heads_kernel(const uint32_t* __restrict__ key, const uint32_t* _
 
 // seg holds the exclusive head count e[k]; turn it into segment ids and emit unique ids / offsets
 __global__ void segments_kernel(const uint32_t* __restrict__ key, uint32_t* hdr, uint32_t* seg, uint32_t* __restrict__ unique,
-                                uint32_t* __restrict__ seg_off, uint32_t n) {
+                                uint32_t* __restrict__ seg_off, uint32_t n, uint32_t tag) {
     const uint32_t kept = hdr[HDR_KEPT];
     const uint32_t n_unique = seg[n];  // flags beyond `kept` are 0, so e[n] is the head total
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < kept; k += gridDim.x * blockDim.x) {
@@ -397,6 +411,7 @@ __global__ void segments_kernel(const uint32_t* __restrict__ key, uint32_t* hdr,
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         hdr[HDR_UNIQUE] = n_unique;
         seg_off[n_unique] = kept;
+        hdr[HDR_TAG] = tag;  // the plan is complete and belongs to this push
     }
 }
 
@@ -429,6 +444,7 @@ __device__ __forceinline__ float upd1(float g_sum, float row, float& acc, float 
 }
 
 struct ApplyArgs {
+    uint32_t tag;  // plan_tag of the push this apply belongs to
     const uint32_t* hdr_ro;
     uint32_t* hdr;
     const uint32_t* perm;
@@ -488,6 +504,10 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     __shared__ float* s_row[256];
     __shared__ float* s_arow[ADAGRAD ? 256 : 1];
     __shared__ uint32_t s_s0[256], s_len[256], s_base[256], s_first[256];
+    if (a.hdr_ro[HDR_TAG] != a.tag) {  // the workspace holds another push's plan (or none): touch nothing
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_MISMATCH] = 1u;
+        return;
+    }
     const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
     const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
     const int dim4 = g.dim / 4;
@@ -497,7 +517,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     const uint32_t ntiles = (n_unique + 255u) / 256u;
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         {  // phase A
-            const uint32_t u = tile + threadIdx.x * ntiles;
+            const uint64_t u = (uint64_t)tile + (uint64_t)threadIdx.x * ntiles;  // 64-bit: no wrap near 2^32 unique ids
             uint32_t s0 = 0, len = 0, cbase = 0, first = 0;
             float* row = nullptr;
             if (u < n_unique) {
@@ -747,6 +767,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     const Workspace ws = carve(const_cast<void*>(d_workspace), n, g.dim);
     const int passes = key_passes(g.rows);
     ApplyArgs a{};
+    a.tag = plan_tag(n, ids_per_worker, geom);
     a.hdr_ro = ws.hdr;
     a.hdr = ws.hdr;
     a.perm = ws.val[(passes - 1) & 1];  // the first pass wrote buffer 0, each later pass flips
@@ -807,8 +828,6 @@ extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_ba
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     const int lg = lane_group(g.dim);
-    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
-    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_GATHER(LG) \
     sparse_gather_kernel<LG><<<resident_grid(sparse_gather_kernel<LG>, 256, (n + 255) / 256), 256, 0, st>>>(d_out, tb, g, d_ids, n)
@@ -819,7 +838,6 @@ extern "C" int b200ps_sparse_gather(float* d_out, const float* const* d_shard_ba
         default: LAUNCH_GATHER(32); break;
     }
 #undef LAUNCH_GATHER
-    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -880,7 +898,8 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     heads_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, (uint32_t)n + 1);
     B200PS_CUDA(scan_exclusive(ws.seg, ws.seg, (uint32_t)n + 1, ws.scan_sums, st, &launches));
-    segments_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, (uint32_t)n);
+    segments_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, (uint32_t)n,
+                                           plan_tag(n, ids_per_worker, geom));
     launches += 2;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add((uint64_t)launches, std::memory_order_relaxed);
@@ -909,6 +928,8 @@ extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total
     uint32_t hdr[HDR_WORDS];
     B200PS_CUDA(cudaMemcpyAsync(hdr, ws.hdr, sizeof hdr, cudaMemcpyDeviceToHost, st));
     B200PS_CUDA(cudaStreamSynchronize(st));
+    B200PS_REQUIRE(hdr[HDR_MISMATCH] == 0, B200PS_ERR_STATE,
+                   "an apply call was given this workspace with another push's (W, ids_per_worker, geometry): it updated nothing");
     const uint32_t kept = hdr[HDR_KEPT], uniq = hdr[HDR_UNIQUE];
     if (n_kept) *n_kept = kept;
     if (n_unique) *n_unique = uniq;
@@ -1119,8 +1140,6 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     const int lg = lane_group(g.dim);
-    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
-    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
     const uint64_t tiles = (n + 255) / 256;
 #define LAUNCH_SERVE(LG) \
@@ -1132,7 +1151,6 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
         default: LAUNCH_SERVE(32); break;
     }
 #undef LAUNCH_SERVE
-    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;
@@ -1157,8 +1175,6 @@ extern "C" int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_id
     int sms = 0;
     B200PS_CUDA(sm_count(&sms));
     const int lg = lane_group(g.dim);
-    const uint64_t want = (n * (uint64_t)lg + 255) / 256;
-    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
     cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_ROUTE(LG) \
     sparse_route_kernel<LG><<<resident_grid(sparse_route_kernel<LG>, 256, (n + 255) / 256), 256, 0, st>>>(ra, d_grad_rows, d_ids, (uint32_t)n, g)
@@ -1169,7 +1185,6 @@ extern "C" int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_id
         default: LAUNCH_ROUTE(32); break;
     }
 #undef LAUNCH_ROUTE
-    (void)grid;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return B200PS_OK;

@@ -121,3 +121,24 @@ def test_placement():
     assert [b200ps.placement_gpu(s, 1) for s in range(3)] == [0, 0, 0]
     with pytest.raises(B200PSError):
         b200ps.placement_gpu(0, 0)
+
+
+def test_json_numbers_and_escapes_follow_the_grammar():
+    """Advisor finding (round 1): numbers go through the JSON grammar before strtod (no 0x10 / inf / nan /
+    leading '+' / '01'), out-of-range doubles are rejected before any integer cast, and a lone or
+    mismatched UTF-16 surrogate in a \\u escape is a parse error instead of invalid UTF-8 in TF_CONFIG."""
+    def job(rep):
+        return '{"metadata":{"name":"a"},"spec":{"replicaSpecs":[{"replicas":%s,"tfReplicaType":"WORKER"}]}}' % rep
+
+    for bad, status in (("0x10", b200ps._lib.ERR_PARSE), ("-inf", b200ps._lib.ERR_PARSE), ("+1", b200ps._lib.ERR_PARSE),
+                        ("01", b200ps._lib.ERR_PARSE), ("1.", b200ps._lib.ERR_PARSE), (".5", b200ps._lib.ERR_PARSE),
+                        ("1e", b200ps._lib.ERR_PARSE), ("1e999", b200ps._lib.ERR_VALIDATION), ("1e300", b200ps._lib.ERR_VALIDATION),
+                        ("2.5", b200ps._lib.ERR_VALIDATION)):
+        with pytest.raises(b200ps.B200PSError) as ei:
+            b200ps.Cluster.from_tfjob(job(bad))
+        assert ei.value.status == status, bad
+    assert [b200ps.Cluster.from_tfjob(job(ok)).num_workers for ok in ("2", "2.0", "2e0", "20e-1")] == [2, 2, 2, 2]
+    for name in ('"\\ud800x"', '"\\ud800\\u0041"', '"\\udc00"'):
+        with pytest.raises(b200ps.B200PSError) as ei:
+            b200ps.Cluster.from_tfjob('{"metadata":{"name":%s},"spec":{"replicaSpecs":[{"replicas":1,"tfReplicaType":"WORKER"}]}}' % name)
+        assert ei.value.status == b200ps._lib.ERR_PARSE

@@ -359,3 +359,28 @@ def test_embedding_table_checkpoint_resume(tmp_path):
         c.load(str(tmp_path))
     for t in (a, b, c):
         t.close()
+
+
+def test_apply_refuses_a_workspace_that_holds_another_push(oracle):
+    """Advisor finding (round 1): apply carves the workspace from its own (W, ids_per_worker) -- given the
+    plan of a different push it used to read garbage offsets.  sort_segment now tags the plan and apply
+    checks the tag on the device: a mismatched call updates nothing and the next plan_read reports it."""
+    rows, S, dim, W, B = 5000, 2, 16, 2, 300
+    rng = np.random.default_rng(11)
+    ids = [dev(rng.integers(0, rows, B)) for _ in range(W)]
+    grads = [torch.ones(B, dim, dtype=torch.float32, device="cuda") for _ in range(W)]
+    table = K.fill_uniform(torch.empty(rows * dim, dtype=torch.float32, device="cuda"), 1, 0, 0).view(rows, dim)
+    before = table.clone()
+    geom = K.table_geom(rows, dim, S)
+    ws = K.sparse_workspace(W * B, dim)
+    K.sparse_sort_segment(ids, B, geom, ws)
+    K.sparse_apply_sgd(shard_views(table, rows, S), [g[:B - 1] for g in grads], B - 1, geom, 0.05, ws)  # another push's shape
+    torch.cuda.synchronize()
+    assert torch.equal(table, before)
+    with pytest.raises(b200ps.B200PSError) as ei:
+        K.sparse_plan_read(ws, W * B, rows)
+    assert ei.value.status == b200ps._lib.ERR_STATE
+    K.sparse_sort_segment(ids, B, geom, ws)  # a fresh plan clears the mark; the matching apply works
+    K.sparse_apply_sgd(shard_views(table, rows, S), grads, B, geom, 0.05, ws)
+    K.sparse_plan_read(ws, W * B, rows)
+    assert not torch.equal(table, before)
