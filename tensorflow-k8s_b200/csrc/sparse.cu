@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     const uint32_t ntiles = (n_unique + 255u) / 256u;
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         {  // phase A
-            const uint64_t u = (uint64_t)tile + (uint64_t)threadIdx.x * ntiles;  // 64-bit: no wrap near 2^32 unique ids
+            const uint32_t u = tile + threadIdx.x * ntiles;  // < n_unique + 256 * ntiles <= 2^32: the entry count is capped below 2^32 - 2^16
             uint32_t s0 = 0, len = 0, cbase = 0, first = 0;
             float* row = nullptr;
             if (u < n_unique) {
@@ -752,7 +752,7 @@ int sparse_apply(float* const* d_shard_base, float* const* d_accum_base, const f
     B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS && d_grad_rows && d_workspace, B200PS_ERR_INVALID,
                    "bad worker count or null argument");
     const uint64_t n = (uint64_t)W * ids_per_worker;
-    B200PS_REQUIRE(n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be below 2^32");
+    B200PS_REQUIRE(n < 0xFFFF0000ull, B200PS_ERR_RANGE, "W * ids_per_worker must be below 2^32 - 2^16");
     if (n == 0) return B200PS_OK;
     ShardBases tb;
     if (int rc = fill_bases(geom, d_shard_base, d_accum_base, &tb)) return rc;
