@@ -4,14 +4,19 @@
 A step = push + aggregate + apply + pull of one synthetic batch of gradients through the dense PS
 path.  Workload = BASELINE.json configs[1] (dense MLP, 100 685 824 fp32 params, Adam): at N=1
 exactly 2 PS shards + 4 workers on one GPU; at N GPUs the same per-GPU density (2N shards, 4N
-workers), i.e. weak scaling, one process per GPU, no host in the data path.
+workers), i.e. weak scaling, one process per GPU.  The parameter server of a rank is built the way a
+launched rank builds it: TFJob spec -> placement -> TF_CONFIG / B200PS_TASKS -> b200ps.rank.job_from_env.
 
   value   worker-steps/s = W x synchronous PS steps/s, gradients resident in HBM (whole job)
-  e2e     the same through ParameterServer.step_host with HOST buffers: H2D of every gradient
-          and D2H of the pulled parameters inside the timed region
-  roofline  the aggregate+apply kernel against the measured HBM copy peak
+  parity_checked  two steps of the same plan on shrunk variables against the oracle, every rank
+  e2e     the training step a user runs: mini-batches H2D from pinned memory, the compute tasks'
+          forward/backward on the GPU (b200ps_mlp_step, tcgen05 GEMMs), the fused PS step, loss D2H;
+          e2e.host_gradients = b200ps_dense_step_host with W host gradient vectors in, parameters out
+  roofline  N=1: the aggregate+apply kernel against the measured HBM copy peak;
+            N>1: the busiest GPU's inbound NVLink bytes against the measured peer-copy rate
+  also    C3, C0 and C2 (uniform / Zipf) measured briefly in the same process
   cpu_baseline / --impl reference  the CPU oracle (a SUBSTITUTE reference: the upstream repo is
-          documentation only) on the box's host cores, all threads
+          documentation only) on the box's host cores, all threads; same `config` as this arm
 
 Prints ONE JSON line on rank 0.
 """
