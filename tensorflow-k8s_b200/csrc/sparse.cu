@@ -117,6 +117,8 @@ __device__ __forceinline__ int gpu_of(const Geom& g, int s) { return s - (int)(g
 // ------------------------------------------------------------------------------------------------
 struct Workspace {
     uint32_t* hdr;
+    uint64_t* lb;         // 4 regions of look-back scan state (tile counter + one word per tile), zeroed with the header
+    uint32_t lb_stride;   // words per region
     uint32_t* key[2];
     uint32_t* val[2];
     uint32_t* hist;       // BINS * nb
@@ -160,6 +162,11 @@ Workspace carve(void* base, uint64_t n, int dim) {
     w.nb = (uint32_t)((n + TILE - 1) / TILE);
     if (w.nb == 0) w.nb = 1;
     w.hdr = (uint32_t*)take(HDR_WORDS * 4);
+    {
+        const size_t longest0 = (size_t)BINS * w.nb > n + 1 ? (size_t)BINS * w.nb : n + 1;
+        w.lb_stride = (uint32_t)((longest0 + SCAN_TILE - 1) / SCAN_TILE + 2);
+        w.lb = (uint64_t*)take((size_t)4 * w.lb_stride * 8);
+    }
     for (int i = 0; i < 2; ++i) w.key[i] = (uint32_t*)take(n * 4);
     for (int i = 0; i < 2; ++i) w.val[i] = (uint32_t*)take(n * 4);
     w.hist = (uint32_t*)take((size_t)BINS * w.nb * 4);
@@ -180,7 +187,7 @@ Workspace carve(void* base, uint64_t n, int dim) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// generic exclusive scan of uint32 (three launches; in place allowed)
+// block-level exclusive scan of uint32 (building block of the single-pass scan below)
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* total) {
     __shared__ uint32_t warp_sums[32];
@@ -208,57 +215,108 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* t
     return inc - x + warp_sums[wid];
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(const uint32_t* __restrict__ in, uint32_t n,
-                                                                   uint32_t* __restrict__ sums) {
-    __shared__ uint32_t total;
-    const uint32_t i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
-    uint32_t s = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (i0 + k < n) s += in[i0 + k];
-    block_exclusive_scan(s, &total);
-    if (threadIdx.x == 0) sums[blockIdx.x] = total;
-}
+// ------------------------------------------------------------------------------------------------
+// Single-pass exclusive scan (decoupled look-back): one launch instead of reduce / sums / down-sweep.
+// Every CTA takes the next tile number from a counter (so a tile only ever waits for tiles that are
+// already running), reduces its tile, publishes (flag, aggregate) as ONE 64-bit word, and warp 0 sums
+// its predecessors' words 32 at a time until it meets one that carries an inclusive prefix.
+// state[0] = tile counter, state[1 + t] = word of tile t: bits 32..33 = 1 aggregate | 2 inclusive.
+// SEG = 1 is the segment pass: the scanned flags are the segment heads of the sorted keys, and the
+// tile emits segment ids, unique ids and segment offsets directly (heads + scan + segments in one launch).
+// ------------------------------------------------------------------------------------------------
+struct SegOut {
+    const uint32_t* key;
+    uint32_t* hdr;
+    uint32_t* seg;
+    uint32_t* unique;
+    uint32_t* seg_off;
+    uint32_t tag;
+};
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_sums_kernel(uint32_t* sums, uint32_t nblk) {
-    __shared__ uint32_t total;
-    uint32_t carry = 0;
-    for (uint32_t base = 0; base < nblk; base += SCAN_THREADS) {
-        const uint32_t i = base + threadIdx.x;
-        const uint32_t x = i < nblk ? sums[i] : 0;
-        const uint32_t e = block_exclusive_scan(x, &total);
-        if (i < nblk) sums[i] = carry + e;
-        carry += total;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) sums[nblk] = carry;  // grand total
+__device__ __forceinline__ uint64_t ld_state(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
 }
+__device__ __forceinline__ void st_state(uint64_t* p, uint64_t v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_down_kernel(const uint32_t* in, uint32_t* out, uint32_t n,
-                                                                 const uint32_t* __restrict__ sums) {
-    __shared__ uint32_t total;
-    const uint32_t i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
-    uint32_t x[4], s = 0;
+template <int SEG>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const uint32_t* in, uint32_t* out, uint32_t n, uint64_t* state,
+                                                                     uint32_t* total_out, const __grid_constant__ SegOut so) {
+    __shared__ uint32_t tile_sh, total, prefix_sh;
+    if (threadIdx.x == 0) tile_sh = atomicAdd(reinterpret_cast<unsigned int*>(state), 1u);
+    __syncthreads();
+    const uint32_t tile = tile_sh, ntiles = gridDim.x;
+    const uint32_t i0 = tile * SCAN_TILE + threadIdx.x * 4;
+    const uint32_t kept = SEG ? so.hdr[HDR_KEPT] : n;
+    uint32_t x[4], kk[4], s = 0;
+    uint32_t prev = 0;
+    if (SEG && i0 > 0 && i0 - 1 < kept) prev = so.key[i0 - 1];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        x[k] = i0 + k < n ? in[i0 + k] : 0;
+        if (SEG) {
+            kk[k] = i0 + k < kept ? so.key[i0 + k] : 0;
+            x[k] = (i0 + k < kept && (i0 + k == 0 || kk[k] != (k ? kk[k - 1] : prev))) ? 1u : 0u;
+        } else {
+            x[k] = i0 + k < n ? in[i0 + k] : 0;
+        }
         s += x[k];
     }
-    uint32_t e = block_exclusive_scan(s, &total) + sums[blockIdx.x];
+    uint32_t e = block_exclusive_scan(s, &total);
+    if (threadIdx.x < 32) {  // warp 0: publish, look back
+        const int lane = threadIdx.x;
+        uint32_t prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_state(state + 1, (2ull << 32) | total);
+        } else {
+            if (lane == 0) st_state(state + 1 + tile, (1ull << 32) | total);
+            int base = (int)tile - 1;
+            for (;;) {
+                const int j = base - lane;
+                uint64_t v = 2ull << 32;  // before tile 0: an inclusive prefix of 0
+                if (j >= 0) do { v = ld_state(state + 1 + j); } while ((v >> 32) == 0);
+                const unsigned inc = __ballot_sync(0xffffffffu, (v >> 32) == 2);
+                const int stop = inc ? __ffs(inc) - 1 : 31;  // nearest predecessor that carries an inclusive prefix
+                uint32_t val = lane <= stop ? (uint32_t)v : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                prefix += val;
+                if (inc) break;
+                base -= 32;
+            }
+            if (lane == 0) st_state(state + 1 + tile, (2ull << 32) | (uint32_t)(prefix + total));
+        }
+        if (lane == 0) {
+            prefix_sh = prefix;
+            if (tile == ntiles - 1) {
+                const uint32_t grand = prefix + total;
+                if (total_out) *total_out = grand;
+                if (SEG) {
+                    so.hdr[HDR_UNIQUE] = grand;
+                    so.seg_off[grand] = kept;
+                    so.hdr[HDR_TAG] = so.tag;  // the plan is complete and belongs to this push
+                }
+            }
+        }
+    }
+    __syncthreads();
+    e += prefix_sh;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (i0 + k < n) out[i0 + k] = e;
+        if (SEG) {
+            if (i0 + k < kept) {
+                const uint32_t sid = e + x[k] - 1u;
+                so.seg[i0 + k] = sid;
+                if (x[k]) {
+                    so.unique[sid] = kk[k];
+                    so.seg_off[sid] = i0 + k;
+                }
+            }
+        } else if (i0 + k < n) {
+            out[i0 + k] = e;
+        }
         e += x[k];
     }
-}
-
-cudaError_t scan_exclusive(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* sums, cudaStream_t st, int* launches) {
-    const uint32_t nblk = (n + SCAN_TILE - 1) / SCAN_TILE;
-    scan_reduce_kernel<<<nblk, SCAN_THREADS, 0, st>>>(in, n, sums);
-    scan_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(sums, nblk);
-    scan_down_kernel<<<nblk, SCAN_THREADS, 0, st>>>(in, out, n, sums);
-    *launches += 3;
-    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -382,37 +440,6 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
         a.val_out[dst] = sval[lp];
     }
     if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = *a.total;  // sum of the histogram = #kept
-}
-
-// ------------------------------------------------------------------------------------------------
-// segments
-// ------------------------------------------------------------------------------------------------
-__global__ void heads_kernel(const uint32_t* __restrict__ key, const uint32_t* __restrict__ hdr, uint32_t* __restrict__ flags,
-                             uint32_t n_plus_1) {
-    const uint32_t kept = hdr[HDR_KEPT];
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n_plus_1; k += gridDim.x * blockDim.x)
-        flags[k] = (k < kept && (k == 0 || key[k] != key[k - 1])) ? 1u : 0u;
-}
-
-// seg holds the exclusive head count e[k]; turn it into segment ids and emit unique ids / offsets
-__global__ void segments_kernel(const uint32_t* __restrict__ key, uint32_t* hdr, uint32_t* seg, uint32_t* __restrict__ unique,
-                                uint32_t* __restrict__ seg_off, uint32_t n, uint32_t tag) {
-    const uint32_t kept = hdr[HDR_KEPT];
-    const uint32_t n_unique = seg[n];  // flags beyond `kept` are 0, so e[n] is the head total
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < kept; k += gridDim.x * blockDim.x) {
-        const bool head = k == 0 || key[k] != key[k - 1];
-        const uint32_t sid = seg[k] + (head ? 1u : 0u) - 1u;
-        seg[k] = sid;
-        if (head) {
-            unique[sid] = key[k];
-            seg_off[sid] = k;
-        }
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        hdr[HDR_UNIQUE] = n_unique;
-        seg_off[n_unique] = kept;
-        hdr[HDR_TAG] = tag;  // the plan is complete and belongs to this push
-    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -866,13 +893,14 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     }
     cudaStream_t st = (cudaStream_t)stream;
     int launches = 0;
-    B200PS_CUDA(cudaMemsetAsync(ws.hdr, 0, HDR_WORDS * 4, st));
+    // header counters and the look-back state of the four scans (contiguous), zeroed together
+    B200PS_CUDA(cudaMemsetAsync(ws.hdr, 0, (size_t)HDR_WORDS * 4 + (size_t)4 * ws.lb_stride * 8, st));
 
     PassArgs a{};
     a.hist = ws.hist;
     a.hdr = ws.hdr;
     a.nb = ws.nb;
-    a.total = ws.scan_sums + (BINS * ws.nb + SCAN_TILE - 1) / SCAN_TILE;
+    a.total = ws.scan_sums;  // grand total of the scanned histogram (written by the scan's last tile)
     // 1 + 2. LSD radix passes, ping-pong between the two buffers; the first one reads the workers'
     // ids and keeps this GPU's entries (key = id, value = source entry w*B + pos)
     const int passes = key_passes(g.rows);
@@ -885,21 +913,24 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
         a.shift = 8 * p;
         if (p == 0) pass_hist_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
         else pass_hist_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-        B200PS_CUDA(scan_exclusive(ws.hist, ws.hist, BINS * ws.nb, ws.scan_sums, st, &launches));
+        {
+            const uint32_t hn = BINS * ws.nb;
+            scan_lookback_kernel<0><<<(hn + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, st>>>(ws.hist, ws.hist, hn, ws.lb + (size_t)p * ws.lb_stride,
+                                                                                              ws.scan_sums, SegOut{});
+            launches += 1;
+        }
         if (p == 0) pass_scatter_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
         else pass_scatter_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
         launches += 2;
         if (p > 0) cur ^= 1;
     }
-    // 3. segments
-    int sms = 0;
-    B200PS_CUDA(sm_count(&sms));
-    const uint64_t want = (n + 1 + 255) / 256;
-    const int grid = (int)(want < (uint64_t)sms * 8 ? want : (uint64_t)sms * 8);
-    heads_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, (uint32_t)n + 1);
-    B200PS_CUDA(scan_exclusive(ws.seg, ws.seg, (uint32_t)n + 1, ws.scan_sums, st, &launches));
-    segments_kernel<<<grid, 256, 0, st>>>(ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, (uint32_t)n,
-                                           plan_tag(n, ids_per_worker, geom));
+    // 3. segment heads, their scan, segment ids / unique ids / offsets: one launch
+    {
+        SegOut so{ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, plan_tag(n, ids_per_worker, geom)};
+        scan_lookback_kernel<1><<<((uint32_t)n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, st>>>(nullptr, nullptr, (uint32_t)n,
+                                                                                                    ws.lb + (size_t)3 * ws.lb_stride, nullptr, so);
+    }
+    launches -= 1;
     launches += 2;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add((uint64_t)launches, std::memory_order_relaxed);

@@ -18,6 +18,7 @@ def main():
     S, W, opt, transport, steps = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3], sys.argv[4], 3
     aggregate = sys.argv[5] if len(sys.argv) > 5 else "flat"
     overlap = (sys.argv[6] == "overlap") if len(sys.argv) > 6 else False
+    ordered_async = (sys.argv[6] == "async") if len(sys.argv) > 6 else False
     graph = (sys.argv[7] == "graph") if len(sys.argv) > 7 else False
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -32,8 +33,17 @@ def main():
     for t in range(1, steps + 1):
         for w in ps.plan.local_workers:
             K.fill_uniform(ps.grad_buffer(w), 2, t, w)
-        ps.step()
         hg = [O.fill_uniform(P, 2, t, w, threads=4) for w in range(W)]
+        if ordered_async:  # every worker's gradient applied on its own, in worker order: W optimizer steps per call
+            ps.step_async_ordered()
+            for w in range(W):
+                k = (t - 1) * W + w + 1
+                if opt == "adam":
+                    O.dense_adam(hp, hm, hv, [hg[w]], O.adam_scalars(1e-3, 0.9, 0.999, 1e-8, k), threads=4, inv_w=np.float32(1.0))
+                else:
+                    O.dense_sgd(hp, [hg[w]], 0.05, threads=4, inv_w=np.float32(1.0))
+            continue
+        ps.step()
         inv_w = np.float32(1.0) / np.float32(W)
         if aggregate in ("two_level", "multimem"):  # the oracle folds per-GPU partials, then the partials
             hg = O.two_level_partials(hg, world, threads=4)

@@ -115,3 +115,13 @@ def test_whole_rank_step_replayed_as_one_cuda_graph(aggregate, mode):
         if not b200ps._lib.lib.b200ps_multicast_supported():
             pytest.skip("the device reports no multicast support")
     _run(2, 4, 8, "adam", "peer", aggregate, mode, "graph")
+
+
+@pytest.mark.parametrize("S,W,opt", [(3, 5, "adam"), (2, 4, "sgd")])
+def test_ordered_async_mode_across_gpus(S, W, opt):
+    """The reproducible stand-in for asynchronous PS training at world = 2: every worker's gradient is
+    applied on its own in worker order (the owner reads it over NVLink), mirrors written with the last one."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    _run(2, S, W, opt, "peer", "flat", "async")
