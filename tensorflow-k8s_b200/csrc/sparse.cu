@@ -13,8 +13,10 @@
 // push on one GPU, all device-side (no host round trip; counts stay in the workspace header):
 //   1. + 2. stable LSD radix sort of the (worker, position)-ordered ids, 8 bits per pass,
 //      ceil(log2(rows)/8) passes, payload = source entry index -> order (id, worker, position);
-//      the first pass reads the workers' ids and keeps only those of this GPU's shards
-//   3. heads + scan -> segment ids, unique ids, segment offsets
+//      the first pass reads the workers' ids and keeps only those of this GPU's shards.  One
+//      pre-pass counts the digits of all passes; each pass is then ONE kernel whose tiles find
+//      their offsets by decoupled look-back over the tiles before them
+//   3. heads + scan -> segment ids, unique ids, segment offsets (one single-pass scan)
 //   4. one lane group per unique id folds its gradient rows in that fixed order (chunks of 256,
 //      see oracle/ps_oracle.c segment_sum), scales by 1/W and updates the row (SGD / Adagrad)
 // Integer outputs are bit-exact against the oracle; the fold order makes the rows bit-exact too.
@@ -33,11 +35,25 @@ namespace b200ps {
 namespace {
 
 constexpr int TILE_THREADS = 256;
-constexpr int ITEMS = 8;
+#ifndef B200PS_SWEEP_ITEMS
+#define B200PS_SWEEP_ITEMS 8
+#endif
+constexpr int ITEMS = B200PS_SWEEP_ITEMS;
 constexpr int TILE = TILE_THREADS * ITEMS;  // entries per CTA in the partition / radix passes
 constexpr int WARPS = TILE_THREADS / 32;
 constexpr int BINS = 256;
-constexpr int SCAN_THREADS = 1024;
+constexpr int MAX_PASSES = 4;  // 32-bit keys, 8 bits per pass
+#ifndef B200PS_SWEEP_LOOKBACK
+#define B200PS_SWEEP_LOOKBACK 8
+#endif
+#ifndef B200PS_SWEEP_MINB
+#define B200PS_SWEEP_MINB 4
+#endif
+constexpr int LOOKBACK = B200PS_SWEEP_LOOKBACK;  // predecessor tiles a radix pass fetches per look-back step
+#ifndef B200PS_SCAN_THREADS
+#define B200PS_SCAN_THREADS 1024
+#endif
+constexpr int SCAN_THREADS = B200PS_SCAN_THREADS;
 constexpr int SCAN_TILE = SCAN_THREADS * 4;
 constexpr uint32_t SEG_CHUNK = 256;  // == PS_SEG_CHUNK of the oracle
 constexpr uint32_t NONE = 0xFFFFFFFFu;
@@ -45,6 +61,8 @@ constexpr uint32_t NONE = 0xFFFFFFFFu;
 enum { HDR_KEPT = 0, HDR_UNIQUE = 1, HDR_BAD = 2, HDR_NLONG = 4, HDR_NCHUNKS = 5,
        HDR_TAG = 8,       // identity of the plan (entries, geometry): written by sort_segment, checked by apply
        HDR_MISMATCH = 9,  // raised by an apply that was given another push's workspace
+       HDR_STUCK = 10,    // a look-back gave up waiting (never expected: a tile only waits for tiles already running)
+       HDR_TICKET = 16,   // tile counters of the radix passes: HDR_TICKET + pass
        HDR_WORDS = 64 };
 
 // Unsigned 32-bit division by a run-time constant without a divide instruction (Granlund &
@@ -117,12 +135,12 @@ __device__ __forceinline__ int gpu_of(const Geom& g, int s) { return s - (int)(g
 // ------------------------------------------------------------------------------------------------
 struct Workspace {
     uint32_t* hdr;
-    uint64_t* lb;         // 4 regions of look-back scan state (tile counter + one word per tile), zeroed with the header
-    uint32_t lb_stride;   // words per region
+    uint32_t* ghist;      // MAX_PASSES x BINS digit counts of the kept keys (pre-pass), zeroed with the header
+    uint64_t* lb;         // look-back state of the segment scan (tile counter + one word per tile), zeroed with the header
+    uint64_t* sweep;      // nb x BINS words: (tile, digit) look-back state of the radix passes, zeroed with the header
+    size_t zero_bytes;    // hdr .. end of sweep
     uint32_t* key[2];
     uint32_t* val[2];
-    uint32_t* hist;       // BINS * nb
-    uint32_t* scan_sums;  // block sums of the generic scan
     uint32_t* seg;        // n + 1: head-count scan, then segment ids
     uint32_t* unique;     // n
     uint32_t* seg_off;    // n + 1
@@ -162,16 +180,12 @@ Workspace carve(void* base, uint64_t n, int dim) {
     w.nb = (uint32_t)((n + TILE - 1) / TILE);
     if (w.nb == 0) w.nb = 1;
     w.hdr = (uint32_t*)take(HDR_WORDS * 4);
-    {
-        const size_t longest0 = (size_t)BINS * w.nb > n + 1 ? (size_t)BINS * w.nb : n + 1;
-        w.lb_stride = (uint32_t)((longest0 + SCAN_TILE - 1) / SCAN_TILE + 2);
-        w.lb = (uint64_t*)take((size_t)4 * w.lb_stride * 8);
-    }
+    w.ghist = (uint32_t*)take((size_t)MAX_PASSES * BINS * 4);
+    w.lb = (uint64_t*)take(((n + 1 + SCAN_TILE - 1) / SCAN_TILE + 2) * 8);
+    w.sweep = (uint64_t*)take((size_t)w.nb * BINS * 8);
+    w.zero_bytes = off;
     for (int i = 0; i < 2; ++i) w.key[i] = (uint32_t*)take(n * 4);
     for (int i = 0; i < 2; ++i) w.val[i] = (uint32_t*)take(n * 4);
-    w.hist = (uint32_t*)take((size_t)BINS * w.nb * 4);
-    const size_t longest = (size_t)BINS * w.nb > n + 1 ? (size_t)BINS * w.nb : n + 1;
-    w.scan_sums = (uint32_t*)take(((longest + SCAN_TILE - 1) / SCAN_TILE + 1) * 4);
     w.seg = (uint32_t*)take((n + 1) * 4);
     w.unique = (uint32_t*)take(n * 4);
     w.seg_off = (uint32_t*)take((n + 1) * 4);
@@ -216,13 +230,14 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* t
 }
 
 // ------------------------------------------------------------------------------------------------
-// Single-pass exclusive scan (decoupled look-back): one launch instead of reduce / sums / down-sweep.
-// Every CTA takes the next tile number from a counter (so a tile only ever waits for tiles that are
-// already running), reduces its tile, publishes (flag, aggregate) as ONE 64-bit word, and warp 0 sums
-// its predecessors' words 32 at a time until it meets one that carries an inclusive prefix.
+// Segment pass: heads + scan + segments in ONE launch (single-pass scan with decoupled look-back).
+// The scanned quantity is the head flag of every sorted key (key differs from the key before it), so
+// the scan inside a warp is ballots and popcounts: warp w of a tile owns 128 consecutive entries,
+// four rounds of 32, lane-consecutive -- every load and store is coalesced.  Every CTA takes the next
+// tile number from a counter (so a tile only ever waits for tiles that are already running),
+// publishes (flag, aggregate) as ONE 64-bit word, and warp 0 sums its predecessors' words 32 at a
+// time until it meets one that carries an inclusive prefix.
 // state[0] = tile counter, state[1 + t] = word of tile t: bits 32..33 = 1 aggregate | 2 inclusive.
-// SEG = 1 is the segment pass: the scanned flags are the segment heads of the sorted keys, and the
-// tile emits segment ids, unique ids and segment offsets directly (heads + scan + segments in one launch).
 // ------------------------------------------------------------------------------------------------
 struct SegOut {
     const uint32_t* key;
@@ -235,36 +250,50 @@ struct SegOut {
 
 __device__ __forceinline__ uint64_t ld_state(const uint64_t* p) {
     uint64_t v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_state(uint64_t* p, uint64_t v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ void st_state(uint64_t* p, uint64_t v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
-template <int SEG>
-__global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const uint32_t* in, uint32_t* out, uint32_t n, uint64_t* state,
-                                                                     uint32_t* total_out, const __grid_constant__ SegOut so) {
-    __shared__ uint32_t tile_sh, total, prefix_sh;
+__global__ void __launch_bounds__(SCAN_THREADS) segment_scan_kernel(uint64_t* state, const __grid_constant__ SegOut so) {
+    __shared__ uint32_t warp_excl[32];
+    __shared__ uint32_t tile_sh, prefix_sh;
     if (threadIdx.x == 0) tile_sh = atomicAdd(reinterpret_cast<unsigned int*>(state), 1u);
+    const uint32_t kept = so.hdr[HDR_KEPT];
     __syncthreads();
     const uint32_t tile = tile_sh, ntiles = gridDim.x;
-    const uint32_t i0 = tile * SCAN_TILE + threadIdx.x * 4;
-    const uint32_t kept = SEG ? so.hdr[HDR_KEPT] : n;
-    uint32_t x[4], kk[4], s = 0;
-    uint32_t prev = 0;
-    if (SEG && i0 > 0 && i0 - 1 < kept) prev = so.key[i0 - 1];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t wbase = tile * SCAN_TILE + wid * 128u;
+    uint32_t kk[4], ball[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (SEG) {
-            kk[k] = i0 + k < kept ? so.key[i0 + k] : 0;
-            x[k] = (i0 + k < kept && (i0 + k == 0 || kk[k] != (k ? kk[k - 1] : prev))) ? 1u : 0u;
-        } else {
-            x[k] = i0 + k < n ? in[i0 + k] : 0;
-        }
-        s += x[k];
+        const uint32_t idx = wbase + k * 32 + lane;
+        kk[k] = idx < kept ? so.key[idx] : 0u;
     }
-    uint32_t e = block_exclusive_scan(s, &total);
-    if (threadIdx.x < 32) {  // warp 0: publish, look back
-        const int lane = threadIdx.x;
+    const uint32_t before = (lane == 0 && wbase > 0 && wbase - 1 < kept) ? so.key[wbase - 1] : 0u;
+    uint32_t wtotal = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t idx = wbase + k * 32 + lane;
+        uint32_t prev = __shfl_up_sync(0xffffffffu, kk[k], 1);
+        const uint32_t last = k ? __shfl_sync(0xffffffffu, kk[k ? k - 1 : 0], 31) : before;
+        if (lane == 0) prev = last;
+        ball[k] = __ballot_sync(0xffffffffu, idx < kept && (idx == 0 || kk[k] != prev));
+        wtotal += __popc(ball[k]);
+    }
+    if (lane == 0) warp_excl[wid] = wtotal;
+    __syncthreads();
+    if (wid == 0) {  // warp 0: scan the warp totals, publish the tile, look back
+        const uint32_t t = lane < SCAN_THREADS / 32 ? warp_excl[lane] : 0u;
+        uint32_t inc = t;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += y;
+        }
+        warp_excl[lane] = inc - t;
+        const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
         uint32_t prefix = 0;
         if (tile == 0) {
             if (lane == 0) st_state(state + 1, (2ull << 32) | total);
@@ -275,13 +304,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const uint3
                 const int j = base - lane;
                 uint64_t v = 2ull << 32;  // before tile 0: an inclusive prefix of 0
                 if (j >= 0) do { v = ld_state(state + 1 + j); } while ((v >> 32) == 0);
-                const unsigned inc = __ballot_sync(0xffffffffu, (v >> 32) == 2);
-                const int stop = inc ? __ffs(inc) - 1 : 31;  // nearest predecessor that carries an inclusive prefix
+                const unsigned inc_mask = __ballot_sync(0xffffffffu, (v >> 32) == 2);
+                const int stop = inc_mask ? __ffs(inc_mask) - 1 : 31;  // nearest predecessor that carries an inclusive prefix
                 uint32_t val = lane <= stop ? (uint32_t)v : 0;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
                 prefix += val;
-                if (inc) break;
+                if (inc_mask) break;
                 base -= 32;
             }
             if (lane == 0) st_state(state + 1 + tile, (2ull << 32) | (uint32_t)(prefix + total));
@@ -290,111 +319,154 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const uint3
             prefix_sh = prefix;
             if (tile == ntiles - 1) {
                 const uint32_t grand = prefix + total;
-                if (total_out) *total_out = grand;
-                if (SEG) {
-                    so.hdr[HDR_UNIQUE] = grand;
-                    so.seg_off[grand] = kept;
-                    so.hdr[HDR_TAG] = so.tag;  // the plan is complete and belongs to this push
-                }
+                so.hdr[HDR_UNIQUE] = grand;
+                so.seg_off[grand] = kept;
+                so.hdr[HDR_TAG] = so.tag;  // the plan is complete and belongs to this push
             }
         }
     }
     __syncthreads();
-    e += prefix_sh;
+    uint32_t e = prefix_sh + warp_excl[wid];  // segments before this warp's first entry
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (SEG) {
-            if (i0 + k < kept) {
-                const uint32_t sid = e + x[k] - 1u;
-                so.seg[i0 + k] = sid;
-                if (x[k]) {
-                    so.unique[sid] = kk[k];
-                    so.seg_off[sid] = i0 + k;
-                }
+        const uint32_t idx = wbase + k * 32 + lane;
+        const uint32_t head = (ball[k] >> lane) & 1u;
+        const uint32_t sid = e + __popc(ball[k] & lt) + head - 1u;
+        if (idx < kept) {
+            so.seg[idx] = sid;
+            if (head) {
+                so.unique[sid] = kk[k];
+                so.seg_off[sid] = idx;
             }
-        } else if (i0 + k < n) {
-            out[i0 + k] = e;
         }
-        e += x[k];
+        e += __popc(ball[k]);
     }
 }
 
 // ------------------------------------------------------------------------------------------------
-// stable radix passes.  MODE 0 = the first pass: reads the workers' ids directly, keeps only the
-// entries of this GPU's shards (a stable partition fused into the pass).  MODE 1 = later passes.
+// Stable LSD radix sort, one kernel per 8-bit pass ("onesweep": Adinets & Merrill).
+//   digit_hist_kernel   one pre-pass over the workers' ids: digit counts of the kept keys for ALL
+//                       passes (a key's digits do not depend on where earlier passes put it).
+//   sweep_pass_kernel   MODE 0 = the first pass: reads the workers' ids directly and keeps only the
+//                       entries of this GPU's shards (a stable partition fused into the pass);
+//                       MODE 1 = later passes.  Every CTA draws its tile number from a counter, ranks
+//                       its 2048 entries, and thread d publishes the tile's count of digit d as one
+//                       64-bit word (flag, count) and sums the words of the tiles before it -- LOOKBACK
+//                       of them in flight at once -- until one carries an inclusive prefix.  A tile only
+//                       waits for tiles with smaller numbers, which are running or done.
+// State word: bits 32.. = 2 * pass + 1 (tile aggregate) | 2 * pass + 2 (inclusive prefix); anything
+// else (zero, or an earlier pass's flag) is "not there yet", so one region serves all passes.
 // ------------------------------------------------------------------------------------------------
-struct PassArgs {
+__global__ void __launch_bounds__(TILE_THREADS) digit_hist_kernel(const __grid_constant__ IdSources src,
+                                                                  const __grid_constant__ Geom g, uint32_t* hdr,
+                                                                  uint32_t* ghist, int passes) {
+    __shared__ uint32_t cnt[MAX_PASSES * BINS];
+    for (int i = threadIdx.x; i < MAX_PASSES * BINS; i += TILE_THREADS) cnt[i] = 0;
+    __syncthreads();
+    uint32_t bad = 0;
+    constexpr int PER = 8;  // ids in flight per thread
+    for (uint64_t i0 = (uint64_t)blockIdx.x * (TILE_THREADS * PER) + threadIdx.x; i0 < src.n_total; i0 += (uint64_t)gridDim.x * (TILE_THREADS * PER)) {
+        int64_t id[PER];
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const uint64_t idx = i0 + (uint64_t)k * TILE_THREADS;
+            id[k] = 0;
+            if (idx < src.n_total) {
+                const uint32_t w = src.by_per_worker.div((uint32_t)idx);
+                id[k] = src.ids[w][(uint32_t)idx - w * src.per_worker];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            if (i0 + (uint64_t)k * TILE_THREADS >= src.n_total) continue;
+            if (id[k] < 0 || (uint64_t)id[k] >= g.rows) {
+                ++bad;
+                continue;
+            }
+            const uint32_t key = (uint32_t)id[k];
+            uint64_t lr;
+            if (gpu_of(g, owner_of(g, (uint64_t)id[k], &lr)) != g.rank) continue;
+            for (int p = 0; p < passes; ++p) atomicAdd(&cnt[p * BINS + ((key >> (8 * p)) & 255u)], 1u);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(&hdr[HDR_BAD], bad);
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * BINS; i += TILE_THREADS)
+        if (cnt[i]) atomicAdd(&ghist[i], cnt[i]);
+}
+
+struct SweepArgs {
     const uint32_t* key_in;
     const uint32_t* val_in;
     uint32_t* key_out;
     uint32_t* val_out;
-    uint32_t* hist;  // BINS x nb, bin-major
-    const uint32_t* total;  // grand total of the scanned histogram (scan_sums[nblk])
+    const uint32_t* ghist;  // this pass's BINS digit counts
+    uint64_t* state;        // [tile][BINS]
     uint32_t* hdr;
-    uint32_t nb;
+    int pass;
     int shift;
 };
 
-// One entry of the tile.  MODE 0 reads the workers' int64 ids, drops (NONE) those that are out of
-// range or belong to another GPU's shards, and takes the lowest 8 key bits; MODE 1 reads the
-// previous pass and takes 8 key bits at `shift`.  Returns the bin or NONE.
 template <int MODE>
-__device__ __forceinline__ uint32_t load_entry(const PassArgs& a, const IdSources& src, const Geom& g, uint32_t idx,
-                                               uint32_t limit, uint32_t* key, uint32_t* val, bool count_bad) {
-    if (idx >= limit) return NONE;
-    if (MODE == 0) {
-        const uint32_t w = src.by_per_worker.div(idx), pos = idx - w * src.per_worker;
-        const int64_t id = src.ids[w][pos];
-        *val = idx;
-        if (id < 0 || (uint64_t)id >= g.rows) {
-            if (count_bad) atomicAdd(&a.hdr[HDR_BAD], 1u);
-            return NONE;
-        }
-        *key = (uint32_t)id;
-        uint64_t lr;
-        return gpu_of(g, owner_of(g, (uint64_t)id, &lr)) == g.rank ? (*key & 255u) : NONE;
-    }
-    *key = a.key_in[idx];
-    *val = a.val_in[idx];
-    return (*key >> a.shift) & 255u;
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(TILE_THREADS) pass_hist_kernel(const __grid_constant__ PassArgs a,
-                                                                 const __grid_constant__ IdSources src,
-                                                                 const __grid_constant__ Geom g) {
-    __shared__ uint32_t cnt[BINS];
-    cnt[threadIdx.x] = 0;
-    __syncthreads();
-    const uint32_t limit = MODE == 0 ? src.n_total : a.hdr[HDR_KEPT];
-    const uint32_t base = blockIdx.x * TILE;
-#pragma unroll
-    for (int b = 0; b < ITEMS; ++b) {
-        uint32_t key, val;
-        const uint32_t d = load_entry<MODE>(a, src, g, base + b * TILE_THREADS + threadIdx.x, limit, &key, &val, true);
-        if (d != NONE) atomicAdd(&cnt[d], 1u);
-    }
-    __syncthreads();
-    a.hist[threadIdx.x * a.nb + blockIdx.x] = cnt[threadIdx.x];
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid_constant__ PassArgs a,
-                                                                    const __grid_constant__ IdSources src,
-                                                                    const __grid_constant__ Geom g) {
+__global__ void __launch_bounds__(TILE_THREADS, B200PS_SWEEP_MINB) sweep_pass_kernel(const __grid_constant__ SweepArgs a,
+                                                                  const __grid_constant__ IdSources src,
+                                                                  const __grid_constant__ Geom g) {
     __shared__ uint32_t cnt[WARPS][BINS];
+    __shared__ uint32_t tile_start[BINS];  // first staged position of each bin
+    __shared__ uint32_t gbase[BINS];       // first global position of (bin, this tile)
+    __shared__ uint32_t skey[TILE], sval[TILE];
+    __shared__ uint32_t tile_sh, kept_sh, tile_total;
     for (int i = threadIdx.x; i < WARPS * BINS; i += TILE_THREADS) (&cnt[0][0])[i] = 0;
-    __syncthreads();
-    const uint32_t limit = MODE == 0 ? src.n_total : a.hdr[HDR_KEPT];
+    if (threadIdx.x == 0) tile_sh = atomicAdd(&a.hdr[HDR_TICKET + a.pass], 1u);
+    // first output position of each digit = exclusive scan of the digit counts; their sum = #kept
+    const uint32_t dbase = block_exclusive_scan(a.ghist[threadIdx.x], &kept_sh);  // ends with a barrier
+    const uint32_t tile = tile_sh, kept = kept_sh;
+    const uint32_t limit = MODE == 0 ? src.n_total : kept;
+    if (MODE == 0 && tile == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = kept;
+    if ((uint64_t)tile * TILE >= limit) return;  // nothing here, and no tile with entries comes after this one
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     // warp w owns entries [w*256, w*256+256) of the tile, 32 consecutive entries per batch: the
     // (batch, lane) order is the input order, which makes the ranks stable
-    const uint32_t base = blockIdx.x * TILE + w * (32 * ITEMS);
+    const uint32_t base = tile * TILE + w * (32 * ITEMS);
     uint32_t key[ITEMS], val[ITEMS], bin[ITEMS], rank[ITEMS];
+    // all of the thread's entries are fetched before the first ranking step: the warp-synchronous
+    // ranking below orders memory operations, so loads issued inside it would complete one by one
+    if (MODE == 0) {
+        int64_t id[ITEMS];
+#pragma unroll
+        for (int b = 0; b < ITEMS; ++b) {
+            const uint32_t idx = base + b * 32 + lane;
+            id[b] = -1;
+            if (idx < limit) {
+                const uint32_t sw = src.by_per_worker.div(idx);
+                id[b] = src.ids[sw][idx - sw * src.per_worker];
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < ITEMS; ++b) {
+            val[b] = base + b * 32 + lane;
+            key[b] = (uint32_t)id[b];
+            bin[b] = NONE;
+            uint64_t lr;
+            if (id[b] >= 0 && (uint64_t)id[b] < g.rows && gpu_of(g, owner_of(g, (uint64_t)id[b], &lr)) == g.rank) bin[b] = key[b] & 255u;
+        }
+    } else {
+#pragma unroll
+        for (int b = 0; b < ITEMS; ++b) {
+            const uint32_t idx = base + b * 32 + lane;
+            key[b] = val[b] = 0;
+            if (idx < limit) {
+                key[b] = a.key_in[idx];
+                val[b] = a.val_in[idx];
+            }
+            bin[b] = idx < limit ? (key[b] >> a.shift) & 255u : NONE;
+        }
+    }
 #pragma unroll
     for (int b = 0; b < ITEMS; ++b) {
-        bin[b] = load_entry<MODE>(a, src, g, base + b * 32 + lane, limit, &key[b], &val[b], false);
         const uint32_t peers = __match_any_sync(0xffffffffu, bin[b]);
         uint32_t start = 0;
         if (bin[b] != NONE) start = cnt[w][bin[b]];
@@ -404,13 +476,6 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
         rank[b] = start + __popc(peers & lt);
     }
     __syncthreads();
-    // Stage the tile in shared memory in (bin, input order) -- its position inside the tile -- and
-    // write it out from there: entries of one bin leave as one contiguous run instead of 32
-    // scattered 4-byte stores per warp instruction (ncu: 30 sectors per store request before).
-    __shared__ uint32_t tile_start[BINS];  // first staged position of each bin
-    __shared__ uint32_t gbase[BINS];       // first global position of (bin, this CTA)
-    __shared__ uint32_t skey[TILE], sval[TILE];
-    __shared__ uint32_t tile_total;
     {
         const int t = threadIdx.x;  // one bin per thread: exclusive offsets over the warps
         uint32_t run = 0;
@@ -420,10 +485,50 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
             cnt[k][t] = run;
             run += c;
         }
-        gbase[t] = a.hist[t * a.nb + blockIdx.x];
+        // publish this tile's count of digit t, then sum the tiles before it
+        uint64_t* const col = a.state + t;
+        const uint32_t fa = 2u * (uint32_t)a.pass + 1u, fi = fa + 1u;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            st_state(col, ((uint64_t)fi << 32) | run);
+        } else {
+            st_state(col + (size_t)tile * BINS, ((uint64_t)fa << 32) | run);
+            const uint64_t* win = col + (size_t)(tile - 1) * BINS;  // nearest predecessor of the window
+            int64_t left = (int64_t)tile;                           // predecessors from `win` down to tile 0
+            uint32_t spins = 0;
+            for (;;) {
+                uint64_t v[LOOKBACK];
+#pragma unroll
+                for (int k = 0; k < LOOKBACK; ++k) v[k] = k < left ? ld_state(win - (size_t)k * BINS) : ((uint64_t)fi << 32);
+                bool ready = true;
+#pragma unroll
+                for (int k = 0; k < LOOKBACK; ++k) ready &= ((uint32_t)(v[k] >> 32) - fa) < 2u;
+                if (!ready) {  // a tile of the window has not published yet: fetch the window again
+                    if (++spins > (1u << 22)) {  // seconds: give up loudly instead of hanging the GPU
+                        a.hdr[HDR_STUCK] = 1u;
+                        break;
+                    }
+                    continue;
+                }
+                bool done = false;
+#pragma unroll
+                for (int k = 0; k < LOOKBACK; ++k) {
+                    excl += done ? 0u : (uint32_t)v[k];
+                    done |= (uint32_t)(v[k] >> 32) == fi;
+                }
+                if (done) break;
+                win -= (size_t)LOOKBACK * BINS;
+                left -= LOOKBACK;
+            }
+            st_state(col + (size_t)tile * BINS, ((uint64_t)fi << 32) | (uint32_t)(excl + run));
+        }
+        gbase[t] = dbase + excl;
         tile_start[t] = block_exclusive_scan(run, &tile_total);  // over the 256 bins; total -> shared
     }
     __syncthreads();
+    // Stage the tile in shared memory in (bin, input order) -- its position inside the tile -- and
+    // write it out from there: entries of one bin leave as one contiguous run instead of 32
+    // scattered 4-byte stores per warp instruction (ncu: 30 sectors per store request before).
 #pragma unroll
     for (int b = 0; b < ITEMS; ++b) {
         if (bin[b] == NONE) continue;
@@ -434,12 +539,11 @@ __global__ void __launch_bounds__(TILE_THREADS) pass_scatter_kernel(const __grid
     __syncthreads();
     for (uint32_t lp = threadIdx.x; lp < tile_total; lp += TILE_THREADS) {
         const uint32_t k = skey[lp];
-        const uint32_t bn = (MODE == 0 ? k : (k >> a.shift)) & 255u;
+        const uint32_t bn = (k >> a.shift) & 255u;
         const uint32_t dst = gbase[bn] + (lp - tile_start[bn]);
         a.key_out[dst] = k;
         a.val_out[dst] = sval[lp];
     }
-    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_KEPT] = *a.total;  // sum of the histogram = #kept
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -519,18 +623,37 @@ __device__ __forceinline__ void update_row(float* row, float* arow, int c, const
 // long_final_kernel, in the chunk order the oracle defines.
 //
 // Two phases per tile of 256 unique ids (like sparse_serve_kernel).  A: one THREAD per unique id
-// reads its segment bounds and id (coalesced), resolves the table row once and leaves a descriptor
-// in shared memory.  B: one LANE GROUP per unique id issues the table-row load, folds the segment's
-// gradient rows in order and writes the row back.
+// reads its segment bounds and id, resolves the table row once and leaves a descriptor in shared
+// memory.  B1: segments of one or two entries (99 % of them for uniform ids) -- one LANE GROUP takes
+// R unique ids at a time, and the R table rows and their gradient rows are all in flight before the
+// first add: this is where the memory parallelism comes from.  B2: the longer segments, one per lane
+// group at a time, folded in order with eight gradient rows in flight.
+//
+// Which ids a tile holds: runs of 8 consecutive unique ids, run j of the table going to tile
+// j mod T (T tiles).  Eight neighbours share the 32-byte sectors of seg_off / unique / perm, so
+// phase A reads ~20 bytes per id instead of four separate sectors; and sorted neighbours -- under
+// Zipf skew the hot ids with their long segments sit together at the front -- are still dealt out
+// over all CTAs instead of landing in one.
+__device__ __forceinline__ uint32_t tile_uid(uint32_t tile, uint32_t r, uint32_t ntiles) {
+    return (tile + (r >> 3) * ntiles) * 8u + (r & 7u);  // < 256 * ntiles < n_unique + 256: the entry count is capped below 2^32 - 2^16
+}
+
+#ifndef B200PS_APPLY_ROWS
+#define B200PS_APPLY_ROWS 4  // unique ids in flight per lane group (phase B1)
+#endif
+#ifndef B200PS_APPLY_MINB
+#define B200PS_APPLY_MINB 3  // resident CTAs per SM the register allocation must allow (R = 4: 72 / 80 registers, no spills)
+#endif
 template <int LG, bool ADAGRAD>
-__global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant__ ShardBases tb,
-                                                           const __grid_constant__ RowSources gs,
-                                                           const __grid_constant__ Geom g,
-                                                           const __grid_constant__ ApplyArgs a) {
+__global__ void __launch_bounds__(256, B200PS_APPLY_MINB) sparse_apply_kernel(const __grid_constant__ ShardBases tb,
+                                                                              const __grid_constant__ RowSources gs,
+                                                                              const __grid_constant__ Geom g,
+                                                                              const __grid_constant__ ApplyArgs a) {
     constexpr int GROUPS = 256 / LG;
+    constexpr int R = B200PS_APPLY_ROWS;
     __shared__ float* s_row[256];
     __shared__ float* s_arow[ADAGRAD ? 256 : 1];
-    __shared__ uint32_t s_s0[256], s_len[256], s_base[256], s_first[256];
+    __shared__ uint32_t s_s0[256], s_len[256], s_base[256], s_first[256], s_second[256];
     if (a.hdr_ro[HDR_TAG] != a.tag) {  // the workspace holds another push's plan (or none): touch nothing
         if (blockIdx.x == 0 && threadIdx.x == 0) a.hdr[HDR_MISMATCH] = 1u;
         return;
@@ -538,19 +661,17 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
     const uint32_t n_unique = a.hdr_ro[HDR_UNIQUE];
     const int lane = threadIdx.x % LG, grp = threadIdx.x / LG;
     const int dim4 = g.dim / 4;
-    // Tile t holds the unique ids t, t + T, t + 2T, ... (T = number of tiles): sorted neighbours --
-    // under Zipf skew the hot ids with their long segments sit together at the front -- are dealt
-    // out over all CTAs instead of landing in one.
     const uint32_t ntiles = (n_unique + 255u) / 256u;
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         {  // phase A
-            const uint32_t u = tile + threadIdx.x * ntiles;  // < n_unique + 256 * ntiles <= 2^32: the entry count is capped below 2^32 - 2^16
-            uint32_t s0 = 0, len = 0, cbase = 0, first = 0;
+            const uint32_t u = tile_uid(tile, threadIdx.x, ntiles);
+            uint32_t s0 = 0, len = 0, cbase = 0, first = 0, second = 0;  // len 0: past the last unique id
             float* row = nullptr;
             if (u < n_unique) {
                 s0 = a.seg_off[u];
                 len = a.seg_off[u + 1] - s0;
-                first = a.perm[s0];  // source entry of the segment's first row: one dependent load less in phase B
+                first = a.perm[s0];  // source entries of the segment's first rows: one dependent load less in phase B
+                if (len >= 2) second = a.perm[s0 + 1];
                 uint64_t lrow;
                 const int s = owner_of(g, a.unique[u], &lrow);
                 row = tb.base[s] + lrow * (uint64_t)g.dim;
@@ -568,17 +689,47 @@ __global__ void __launch_bounds__(256) sparse_apply_kernel(const __grid_constant
             s_len[threadIdx.x] = len;
             s_base[threadIdx.x] = cbase;
             s_first[threadIdx.x] = first;
+            s_second[threadIdx.x] = second;
         }
         __syncthreads();
-        for (int r = grp; r < 256; r += GROUPS) {  // phase B
+        for (int r0 = grp; r0 < 256; r0 += GROUPS * R) {  // phase B1: one or two entries
+            for (int c = lane; c < dim4; c += LG) {
+                float4 rv[R], ac[R], g0[R], g1[R];
+#pragma unroll
+                for (int k = 0; k < R; ++k) {
+                    const int r = r0 + k * GROUPS;
+                    const uint32_t len = r < 256 ? s_len[r] : 0u;
+                    rv[k] = ac[k] = g0[k] = g1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (len - 1u >= 2u) continue;
+                    rv[k] = reinterpret_cast<const float4*>(s_row[r])[c];
+                    if (ADAGRAD) ac[k] = reinterpret_cast<const float4*>(s_arow[r])[c];
+                    g0[k] = ldg_row4(grad_row(gs, s_first[r], g.dim), c);
+                    if (len == 2u) g1[k] = ldg_row4(grad_row(gs, s_second[r], g.dim), c);
+                }
+#pragma unroll
+                for (int k = 0; k < R; ++k) {
+                    const int r = r0 + k * GROUPS;
+                    const uint32_t len = r < 256 ? s_len[r] : 0u;
+                    if (len - 1u >= 2u) continue;
+                    const float4 acc = len == 2u ? add4(g0[k], g1[k]) : g0[k];
+                    rv[k].x = upd1<ADAGRAD>(acc.x, rv[k].x, ac[k].x, a.inv_w, a.lr);
+                    rv[k].y = upd1<ADAGRAD>(acc.y, rv[k].y, ac[k].y, a.inv_w, a.lr);
+                    rv[k].z = upd1<ADAGRAD>(acc.z, rv[k].z, ac[k].z, a.inv_w, a.lr);
+                    rv[k].w = upd1<ADAGRAD>(acc.w, rv[k].w, ac[k].w, a.inv_w, a.lr);
+                    reinterpret_cast<float4*>(s_row[r])[c] = rv[k];
+                    if (ADAGRAD) reinterpret_cast<float4*>(s_arow[r])[c] = ac[k];
+                }
+            }
+        }
+        for (int r = grp; r < 256; r += GROUPS) {  // phase B2: three entries and more
             const uint32_t s0 = s_s0[r], len = s_len[r];
-            float* row = s_row[r];
-            if (row == nullptr) continue;  // past the last unique id
-            if (len > SEG_CHUNK) {
+            if (len < 3u) continue;
+            if (len > SEG_CHUNK) {  // a hot id: register its chunks, the long kernels do the rest
                 const uint32_t nchunks = (len + SEG_CHUNK - 1) / SEG_CHUNK, cbase = s_base[r];
-                for (uint32_t jj = lane; jj < nchunks; jj += LG) a.chunks[cbase + jj] = make_uint2(tile + (uint32_t)r * ntiles, jj);
+                for (uint32_t jj = lane; jj < nchunks; jj += LG) a.chunks[cbase + jj] = make_uint2(tile_uid(tile, (uint32_t)r, ntiles), jj);
                 continue;
             }
+            float* row = s_row[r];
             float* arow = ADAGRAD ? s_arow[r] : nullptr;
             for (int c = lane; c < dim4; c += LG) {
                 // the row being updated does not depend on the fold: get it in flight first
@@ -878,7 +1029,7 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     B200PS_REQUIRE(W >= 1 && W <= B200PS_MAX_WORKERS && d_ids && d_workspace, B200PS_ERR_INVALID,
                    "bad worker count or null argument");
     const uint64_t n = (uint64_t)W * ids_per_worker;
-    B200PS_REQUIRE(n >= 1 && n < 0xFFFFFFFFull, B200PS_ERR_RANGE, "W * ids_per_worker must be in 1..2^32-2");
+    B200PS_REQUIRE(n >= 1 && n < 0xFFFF0000ull, B200PS_ERR_RANGE, "W * ids_per_worker must be in 1..2^32-2^16-1");
     B200PS_REQUIRE(((uintptr_t)d_workspace & 255) == 0, B200PS_ERR_INVALID, "workspace must be 256-byte aligned");
     const Workspace ws = carve(d_workspace, n, g.dim);
     B200PS_REQUIRE(workspace_bytes >= ws.bytes, B200PS_ERR_RANGE, "workspace of %zu bytes is too small: %zu needed",
@@ -893,45 +1044,44 @@ extern "C" int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, ui
     }
     cudaStream_t st = (cudaStream_t)stream;
     int launches = 0;
-    // header counters and the look-back state of the four scans (contiguous), zeroed together
-    B200PS_CUDA(cudaMemsetAsync(ws.hdr, 0, (size_t)HDR_WORDS * 4 + (size_t)4 * ws.lb_stride * 8, st));
+    // header counters, digit counts and all look-back state (contiguous), zeroed together
+    B200PS_CUDA(cudaMemsetAsync(ws.hdr, 0, ws.zero_bytes, st));
 
-    PassArgs a{};
-    a.hist = ws.hist;
-    a.hdr = ws.hdr;
-    a.nb = ws.nb;
-    a.total = ws.scan_sums;  // grand total of the scanned histogram (written by the scan's last tile)
+    // 0. digit counts of the kept keys, all passes at once
+    const int passes = key_passes(g.rows);
+    {
+        int sms = 0;
+        B200PS_CUDA(sm_count(&sms));
+        const uint32_t want = (uint32_t)((n + TILE_THREADS * 8 - 1) / (TILE_THREADS * 8));  // 8 entries per thread and iteration
+        const uint32_t grid = want < (uint32_t)(4 * sms) ? want : (uint32_t)(4 * sms);
+        digit_hist_kernel<<<grid, TILE_THREADS, 0, st>>>(src, g, ws.hdr, ws.ghist, passes);
+        launches += 1;
+    }
     // 1 + 2. LSD radix passes, ping-pong between the two buffers; the first one reads the workers'
     // ids and keeps this GPU's entries (key = id, value = source entry w*B + pos)
-    const int passes = key_passes(g.rows);
+    SweepArgs a{};
+    a.state = ws.sweep;
+    a.hdr = ws.hdr;
     int cur = 0;
     for (int p = 0; p < passes; ++p) {
         a.key_in = ws.key[cur];
         a.val_in = ws.val[cur];
         a.key_out = ws.key[p == 0 ? 0 : cur ^ 1];
         a.val_out = ws.val[p == 0 ? 0 : cur ^ 1];
+        a.ghist = ws.ghist + p * BINS;
+        a.pass = p;
         a.shift = 8 * p;
-        if (p == 0) pass_hist_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-        else pass_hist_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-        {
-            const uint32_t hn = BINS * ws.nb;
-            scan_lookback_kernel<0><<<(hn + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, st>>>(ws.hist, ws.hist, hn, ws.lb + (size_t)p * ws.lb_stride,
-                                                                                              ws.scan_sums, SegOut{});
-            launches += 1;
-        }
-        if (p == 0) pass_scatter_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-        else pass_scatter_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
-        launches += 2;
+        if (p == 0) sweep_pass_kernel<0><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        else sweep_pass_kernel<1><<<ws.nb, TILE_THREADS, 0, st>>>(a, src, g);
+        launches += 1;
         if (p > 0) cur ^= 1;
     }
     // 3. segment heads, their scan, segment ids / unique ids / offsets: one launch
     {
         SegOut so{ws.key[cur], ws.hdr, ws.seg, ws.unique, ws.seg_off, plan_tag(n, ids_per_worker, geom)};
-        scan_lookback_kernel<1><<<((uint32_t)n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, st>>>(nullptr, nullptr, (uint32_t)n,
-                                                                                                    ws.lb + (size_t)3 * ws.lb_stride, nullptr, so);
+        segment_scan_kernel<<<((uint32_t)n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, st>>>(ws.lb, so);
+        launches += 1;
     }
-    launches -= 1;
-    launches += 2;
     B200PS_CUDA(cudaGetLastError());
     g_launches.fetch_add((uint64_t)launches, std::memory_order_relaxed);
     return B200PS_OK;
@@ -961,6 +1111,7 @@ extern "C" int b200ps_sparse_plan_read(const void* d_workspace, uint64_t n_total
     B200PS_CUDA(cudaStreamSynchronize(st));
     B200PS_REQUIRE(hdr[HDR_MISMATCH] == 0, B200PS_ERR_STATE,
                    "an apply call was given this workspace with another push's (W, ids_per_worker, geometry): it updated nothing");
+    B200PS_REQUIRE(hdr[HDR_STUCK] == 0, B200PS_ERR_STATE, "a radix pass gave up waiting for an earlier tile: the plan is not valid");
     const uint32_t kept = hdr[HDR_KEPT], uniq = hdr[HDR_UNIQUE];
     if (n_kept) *n_kept = kept;
     if (n_unique) *n_unique = uniq;
@@ -1173,8 +1324,9 @@ extern "C" int b200ps_sparse_serve(float* const* d_out, const float* const* d_sh
     const int lg = lane_group(g.dim);
     cudaStream_t st = (cudaStream_t)stream;
     const uint64_t tiles = (n + 255) / 256;
-#define LAUNCH_SERVE(LG) \
-    sparse_serve_kernel<LG><<<resident_grid(sparse_serve_kernel<LG>, 256, tiles), 256, 0, st>>>(sa, tb, src, g)
+    // one CTA per tile rather than a resident grid: measured a little faster, and slots free up all the
+    // time for the sort of a table step that runs beside this kernel (table.cu)
+#define LAUNCH_SERVE(LG) sparse_serve_kernel<LG><<<(unsigned)tiles, 256, 0, st>>>(sa, tb, src, g)
     switch (lg) {
         case 4: LAUNCH_SERVE(4); break;
         case 8: LAUNCH_SERVE(8); break;

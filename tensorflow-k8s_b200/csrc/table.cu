@@ -16,6 +16,9 @@
 //   pull  barrier -> serve (every owner serves its rows into the requesting tasks' buffers) -> barrier
 //   push  route (rows owned elsewhere go to the owners' staging slots) -> barrier ->
 //         sort_segment -> apply -> barrier
+//   step  (pull + push of the same ids as one unit) the push plan needs the ids only, so sort_segment
+//         runs on a second, high-priority stream BESIDE serve and route and joins before apply:
+//         barrier -> { serve -> route -> barrier | sort_segment } -> apply -> barrier
 #include <cuda_runtime.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -144,6 +147,8 @@ struct b200ps_table {
     std::vector<const int64_t*> ids_ptrs;
     std::vector<std::vector<float*>> route_dst;  // per local task: staging slot on every GPU (null for this one)
     cudaStream_t s_cap = nullptr;
+    cudaStream_t s_side = nullptr;                 // the plan of a step is made here, beside the pull
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaGraphExec_t graph = nullptr;
     uint64_t graph_kernels = 0;
     bool profile = false;
@@ -279,6 +284,31 @@ int enqueue_push(b200ps_table* t, cudaStream_t st) {
     return tbarrier(t, st);  // every shard is updated before anyone pulls again
 }
 
+// pull + push of the same ids as one unit.  The barrier that closes the pull and the one that guards
+// the push are the same one (the routed rows and the served rows land behind it together), and the
+// push plan is made on the side stream while the rows are being served.  With phase timing on, the
+// phases run one after the other so that each span means what its name says.
+int enqueue_step(b200ps_table* t, cudaStream_t st) {
+    if (t->profile) {
+        if (int rc = enqueue_pull(t, st, false)) return rc;
+        return enqueue_push(t, st);
+    }
+    if (int rc = tbarrier(t, st)) return rc;  // every task's ids are written
+    B200PS_CUDA(cudaEventRecord(t->ev_fork, st));
+    B200PS_CUDA(cudaStreamWaitEvent(t->s_side, t->ev_fork, 0));
+    int rc = do_sort(t, t->s_side);
+    const cudaError_t e1 = cudaEventRecord(t->ev_join, t->s_side);
+    if (!rc) rc = do_serve(t, st);
+    if (!rc) rc = do_route(t, st);
+    if (!rc) rc = tbarrier(t, st);  // every served and every routed row has landed
+    const cudaError_t e2 = cudaStreamWaitEvent(st, t->ev_join, 0);  // always joined: a capture must not end with a loose branch
+    if (rc) return rc;
+    B200PS_CUDA(e1);
+    B200PS_CUDA(e2);
+    if (int rc2 = do_apply(t, st)) return rc2;
+    return tbarrier(t, st);  // every shard is updated before anyone pulls again
+}
+
 std::string tbl_path(const b200ps_table* t, const char* dir) {
     return std::string(dir) + "/table-rank" + std::to_string(t->rank) + "-of-" + std::to_string(t->world) + ".b200ps";
 }
@@ -355,6 +385,14 @@ extern "C" int b200ps_table_create(const b200ps_cluster_t* cluster, uint64_t row
     *t->host_abort = 0;
     B200PS_CUDA(cudaHostGetDevicePointer(&t->host_abort_dev, t->host_abort, 0));
     B200PS_CUDA(cudaStreamCreateWithFlags(&t->s_cap, cudaStreamNonBlocking));
+    {
+        int least = 0, greatest = 0;
+        B200PS_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        // the sort is a chain of short, latency-bound kernels: its CTAs go first whenever a slot frees up
+        B200PS_CUDA(cudaStreamCreateWithPriority(&t->s_side, cudaStreamNonBlocking, greatest));
+        B200PS_CUDA(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
+        B200PS_CUDA(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
+    }
     if (t->L.adagrad) {  // TF's initial_accumulator_value
         for (int s : t->local_shards) {
             const size_t n = (size_t)(t->L.shard_range[(size_t)s].second - t->L.shard_range[(size_t)s].first) * (size_t)dim;
@@ -376,6 +414,9 @@ extern "C" int b200ps_table_destroy(b200ps_table_t* t) {
         if (t->base[r] && t->base[r] != t->arena) cudaIpcCloseMemHandle(t->base[r]);
     for (cudaEvent_t e : t->event_pool) cudaEventDestroy(e);
     if (t->s_cap) cudaStreamDestroy(t->s_cap);
+    if (t->s_side) cudaStreamDestroy(t->s_side);
+    if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+    if (t->ev_join) cudaEventDestroy(t->ev_join);
     cudaFree(t->workspace);
     cudaFree(t->st);
     cudaFreeHost(t->host_abort);
@@ -456,8 +497,7 @@ extern "C" int b200ps_sparse_push(b200ps_table_t* t, void* stream) {
     return enqueue_push(t, (cudaStream_t)stream);
 }
 
-// pull of all tasks + push, as one unit: the barrier that closes the pull and the one that guards the push
-// are the same one (the routed rows and the served rows land behind it together)
+// pull of all tasks + push, as one unit (enqueue_step)
 extern "C" int b200ps_sparse_step(b200ps_table_t* t, void* stream) {
     if (int rc = alive(t)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -465,8 +505,7 @@ extern "C" int b200ps_sparse_step(b200ps_table_t* t, void* stream) {
         if (!t->graph) {
             cudaGraph_t g = nullptr;
             B200PS_CUDA(cudaStreamBeginCapture(t->s_cap, cudaStreamCaptureModeThreadLocal));
-            int rc = enqueue_pull(t, t->s_cap, false);
-            if (!rc) rc = enqueue_push(t, t->s_cap);
+            const int rc = enqueue_step(t, t->s_cap);
             const cudaError_t e = cudaStreamEndCapture(t->s_cap, &g);
             if (rc) {
                 if (g) cudaGraphDestroy(g);
@@ -490,8 +529,7 @@ extern "C" int b200ps_sparse_step(b200ps_table_t* t, void* stream) {
         g_launches.fetch_add(t->graph_kernels, std::memory_order_relaxed);
         return B200PS_OK;
     }
-    if (int rc = enqueue_pull(t, st, false)) return rc;
-    return enqueue_push(t, st);
+    return enqueue_step(t, st);
 }
 
 extern "C" int b200ps_table_set_graph(b200ps_table_t* t, int on) {
