@@ -125,8 +125,12 @@ class ClockSampler(threading.Thread):
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
                0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
 
-    def __init__(self, device_index: int):
+    def __init__(self, device_index: int, interval: float = 0.02):
         super().__init__(daemon=True)
+        # Every NVML query stalls its GPU for a moment, and with N ranks in lock-step (peer barriers) every stall
+        # of any GPU is everyone's: at N = 8, sampling each GPU every 5 ms cost the step 4-10 % (tools/n8_variants.py:
+        # 1.20 -> 1.25-1.32 ms).  So: one sample at once, then one every `interval` seconds (0.04 s at N > 2).
+        self.interval = interval
         self.samples, self.reasons, self.max_mhz, self._halt = [], set(), None, threading.Event()
         self.err = None
         try:
@@ -158,7 +162,13 @@ class ClockSampler(threading.Thread):
             except Exception as e:
                 self.err = repr(e)
                 return
-            time.sleep(0.005)
+            self._halt.wait(self.interval)
+
+    def mark(self):
+        """The timed region starts here: keep only what is sampled from now on.  (The thread is started before the
+        warm-up steps because the FIRST NVML queries are the expensive ones -- with N ranks in lock-step they cost the
+        timed region 12-15 ms when the sampler was started right at its beginning.)"""
+        self.samples, self.reasons = [], set()
 
     def finish(self):
         self._halt.set()
@@ -354,7 +364,7 @@ def sparse_measure(args, ids_kind, steps, warmup, e2e=False, cpu=False, graph=Tr
             tab.step()
         sync()
         plan = tab.plan()
-        sampler = ClockSampler(local)
+        sampler = ClockSampler(local, 0.02 if world <= 2 else 0.04)
         sampler.start()
         l0 = K.launch_count()
         launched_ms = timed(steps)
@@ -463,7 +473,9 @@ def make_ps(name, args, rank, world, graph=False, scale=1, aggregate=None):
     if agg == "auto":
         agg = "multimem" if world >= 4 and b200ps._lib.lib.b200ps_multicast_supported() else "two_level"
     if ov == "auto":  # pipelining pays when the fold is long enough to hide something (C1: 0.32 ms); not for C3-sized sets
-        ov = "on" if world > 1 and (agg == "multimem" or world == 2) and full_params >= 50_000_000 else "off"
+        ov = getattr(args, "overlap_tuned", {}).get(name)  # measured on this box by tune_overlap(), when it ran
+        if ov is None:
+            ov = "on" if world == 2 and full_params >= 50_000_000 else "off"
     cluster = b200ps.Cluster.from_tfjob(tfjob_spec(name, S, W))
     env = launcher.rank_env(launcher.plan_tasks(cluster, world), rank, world, int(os.environ.get("MASTER_PORT", "29500")))
     job = rankmod.job_from_env({**env, "RANK": str(rank), "WORLD_SIZE": str(world)})
@@ -472,6 +484,54 @@ def make_ps(name, args, rank, world, graph=False, scale=1, aggregate=None):
                                 world=world, transport=args.transport, aggregate=agg, overlap=ov == "on",
                                 use_graph=graph, cluster=job.cluster)
     return ps, label, sizes, S, W, opt
+
+
+def tune_overlap(name, args, rank, world, steps=20):
+    """N > 1 and --overlap auto: which step form is faster on THIS box?  The sequential form (fold -> barrier ->
+    applies -> barrier) is steady (C1 multimem: 1.24 / 1.20 ms at N = 4 / 8); the pipelined form (fold publishes
+    unit after unit, applies wait in their prologue) depends on how the two kernels share the SMs and was measured
+    anywhere between 1.11 and 1.51 ms at N = 4 on different boxes.  So both are timed (10 warm-up + `steps` steps,
+    CUDA events, max over ranks -- every rank sees the same numbers and takes the same decision) and the faster one
+    is used for the parity pre-check, the timed run and the e2e leg.  Returns what it measured, or None."""
+    import torch
+    import torch.distributed as dist
+
+    from b200ps import kernels as K
+
+    _, sizes, _, _, _ = workload(name, world)
+    if world == 1 or args.overlap != "auto" or args.transport != "peer" or sum(sizes) < 50_000_000:
+        return None
+    seen = {}
+    for ov in ("off", "on"):
+        args.overlap_tuned = {name: ov}
+        ps, *_ = make_ps(name, args, rank, world)
+        ps.init_uniform(1)
+        for w in ps.plan.local_workers:
+            K.fill_uniform(ps.grad_buffer(w), 2, 1, w)
+        with torch.cuda.stream(torch.cuda.Stream()):
+            for _ in range(10):
+                ps.step()
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(steps):
+                ps.step()
+            b.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([a.elapsed_time(b) / steps], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        seen[ov] = float(t.item())
+        ps.check_barriers()
+        ps.close()
+        del ps
+        torch.cuda.empty_cache()
+        dist.barrier()
+    best = "on" if seen["on"] < 0.97 * seen["off"] else "off"  # the pipelined form must win clearly: it is the less steady one
+    args.overlap_tuned = {name: best}
+    return {"sequential_ms": round(seen["off"], 4), "pipelined_ms": round(seen["on"], 4), "chosen": "pipelined" if best == "on" else "sequential",
+            "steps": steps}
 
 
 def parity_check(name, args, rank, world, steps=2, scale=64):
@@ -584,11 +644,12 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
     stream = torch.cuda.Stream()  # a real stream: the step is ordered on it (the legacy default stream serialises)
     sync()
     with torch.cuda.stream(stream):
+        sampler = ClockSampler(local, 0.02 if world <= 2 else 0.04)
+        sampler.start()
         for _ in range(warmup):
             ps.step()
         sync()
-        sampler = ClockSampler(local)
-        sampler.start()
+        sampler.mark()
         launches0 = K.launch_count()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         host_t0 = time.perf_counter()
@@ -669,12 +730,14 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
         P = ps.plan.P
         n_e2e = args.e2e_steps or min(steps, 30)
 
-        def timed_host_loop(fn, tail, n=None):
+        def timed_host_loop(fn, tail, n=None, sampler=None):
             n = n or n_e2e
             with torch.cuda.stream(stream):
                 for _ in range(5):
                     fn()
                 sync()
+                if sampler:
+                    sampler.mark()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
                 for _ in range(n):
@@ -716,10 +779,10 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
                 wk.step(hx, ht)  # H2D of the mini-batches, forward/backward of the local tasks, loss D2H
                 ps.step()        # push (zero-copy) + aggregate + apply + pull (zero-copy)
 
-            smp = ClockSampler(local)
+            smp = ClockSampler(local, 0.02 if world <= 2 else 0.04)
             smp.start()
             n_train = args.e2e_steps or min(steps, 100)
-            t_ms = timed_host_loop(train_step, lambda: None, n_train)
+            t_ms = timed_host_loop(train_step, lambda: None, n_train, sampler=smp)
             e2e_clocks = smp.finish()
             w_ms = timed_host_loop(lambda: wk.step(hx, ht), lambda: None)  # the worker half alone, for the breakdown
             losses = [float(v) for v in wk.loss]
@@ -779,9 +842,11 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     warm = max(args.warmup, 3)
+    tuned = tune_overlap(args.workload, args, rank, world)
     parity = parity_check(args.workload, args, rank, world)
     out = measure_dense(args.workload, args, rank, world, local, args.steps, warm, e2e=not args.no_e2e, cpu=not args.no_cpu)
     out["parity_checked"] = parity
+    out["impl_config"]["step_form_autotune"] = tuned
     out.setdefault("cpu_baseline", None)
     out.setdefault("e2e", None)
     # ---- the other BASELINE configs, briefly, in the same process (not the headline) ----

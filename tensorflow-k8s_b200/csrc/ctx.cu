@@ -100,6 +100,7 @@ struct b200ps_ctx {
     std::vector<Span> spans[3];  // fold, apply, barrier
     std::vector<cudaEvent_t> event_pool;
     std::vector<cudaEvent_t> phase_ev;
+    int phase_ev_mode = 0;
 
     uint32_t* flags_of(int r) const { return reinterpret_cast<uint32_t*>(base[r] + plan->arena_elems(r)); }
     bool adam() const { return o.optimizer == B200PS_OPT_ADAM; }
@@ -212,6 +213,8 @@ int launch_apply(b200ps_ctx* c, size_t i, uint64_t lo, uint64_t hi, uint64_t t_s
         a.p_mc = mc + lo;
         a.p = c->arena + lo;
         a.n = hi - lo;
+        if (const char* rot = getenv("B200PS_MC_ROTATE"))  // experiment knob: rank-dependent start of the walk
+            if (atoi(rot)) a.rot4 = ((uint64_t)p.rank * (a.n / 4) / (uint64_t)p.world) & ~7ull;
         a.inv_w = c->inv_w;
         a.abort_word = &c->st->abort;
         if (wait_unit >= 0) {
@@ -371,15 +374,21 @@ int enqueue_step_pipelined(b200ps_ctx* c, cudaStream_t st) {
     return barrier(c, st, true);
 }
 
-// experiment knob (B200PS_STEP_EVENTS = 1 | 2): an event record behind every phase of the sequential step
+// experiment knob (B200PS_STEP_EVENTS = 1 | 2 | 3): event records behind every phase of the sequential step
+// (1: without timing, 2: with timing, 3: two timing events back to back, as the profile pass leaves them)
 void phase_event(b200ps_ctx* c, cudaStream_t st, int k) {
-    static const int mode = getenv("B200PS_STEP_EVENTS") ? atoi(getenv("B200PS_STEP_EVENTS")) : 0;
+    const char* env = getenv("B200PS_STEP_EVENTS");
+    const int mode = env ? atoi(env) : 0;
     if (!mode || c->profile) return;
-    if (c->phase_ev.size() < 4) {
-        c->phase_ev.resize(4, nullptr);
-        for (auto& e : c->phase_ev) cudaEventCreateWithFlags(&e, mode == 2 ? cudaEventDefault : cudaEventDisableTiming);
+    if (c->phase_ev.size() < 8 || c->phase_ev_mode != mode) {
+        for (auto& e : c->phase_ev)
+            if (e) cudaEventDestroy(e);
+        c->phase_ev.assign(8, nullptr);
+        for (auto& e : c->phase_ev) cudaEventCreateWithFlags(&e, mode == 1 ? cudaEventDisableTiming : cudaEventDefault);
+        c->phase_ev_mode = mode;
     }
     cudaEventRecord(c->phase_ev[(size_t)k], st);
+    if (mode == 3) cudaEventRecord(c->phase_ev[(size_t)k + 4], st);
 }
 
 int enqueue_step(b200ps_ctx* c, cudaStream_t st) {

@@ -311,17 +311,21 @@ __global__ void __launch_bounds__(256) dense_apply_mc_kernel(const __grid_consta
     }
     const float lr = a.lr;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, n4 = a.n / 4;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
-        const bool two = i + stride < n4;
+    for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += 2 * stride) {
+        const bool two = i0 + stride < n4;
+        // the ranks walk their slices from different relative offsets (rot4), wrapping around
+        uint64_t i = i0 + a.rot4, j = i0 + stride + a.rot4;
+        if (i >= n4) i -= n4;
+        if (j >= n4) j -= n4;
         float4 s0 = mc_ld_reduce(reinterpret_cast<const float4*>(a.g_mc) + i), s1 = s0;
-        if (two) s1 = mc_ld_reduce(reinterpret_cast<const float4*>(a.g_mc) + i + stride);
+        if (two) s1 = mc_ld_reduce(reinterpret_cast<const float4*>(a.g_mc) + j);
         float4 P0 = ld_state(reinterpret_cast<const float4*>(a.p) + i), P1 = P0, M0 = P0, M1 = P0, V0 = P0, V1 = P0;
         if (HAS_M(OPT)) M0 = ld_state(reinterpret_cast<const float4*>(a.m) + i);
         if (HAS_V(OPT)) V0 = ld_state(reinterpret_cast<const float4*>(a.v) + i);
         if (two) {
-            P1 = ld_state(reinterpret_cast<const float4*>(a.p) + i + stride);
-            if (HAS_M(OPT)) M1 = ld_state(reinterpret_cast<const float4*>(a.m) + i + stride);
-            if (HAS_V(OPT)) V1 = ld_state(reinterpret_cast<const float4*>(a.v) + i + stride);
+            P1 = ld_state(reinterpret_cast<const float4*>(a.p) + j);
+            if (HAS_M(OPT)) M1 = ld_state(reinterpret_cast<const float4*>(a.m) + j);
+            if (HAS_V(OPT)) V1 = ld_state(reinterpret_cast<const float4*>(a.v) + j);
         }
         apply4<OPT>(s0, P0, M0, V0, a, lr);
         mc_st(reinterpret_cast<float4*>(a.p_mc) + i, P0);
@@ -329,9 +333,9 @@ __global__ void __launch_bounds__(256) dense_apply_mc_kernel(const __grid_consta
         if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + i, V0);
         if (two) {
             apply4<OPT>(s1, P1, M1, V1, a, lr);
-            mc_st(reinterpret_cast<float4*>(a.p_mc) + i + stride, P1);
-            if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + i + stride, M1);
-            if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + i + stride, V1);
+            mc_st(reinterpret_cast<float4*>(a.p_mc) + j, P1);
+            if (HAS_M(OPT)) st_f4(reinterpret_cast<float4*>(a.m) + j, M1);
+            if (HAS_V(OPT)) st_f4(reinterpret_cast<float4*>(a.v) + j, V1);
         }
     }
 }

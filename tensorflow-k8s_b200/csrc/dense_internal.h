@@ -53,6 +53,7 @@ struct McApply {
     float* m = nullptr;
     float* v = nullptr;
     uint64_t n = 0;
+    uint64_t rot4 = 0;            // the walk over the slice starts here (float4 units) and wraps around
     float inv_w = 1.f, lr = 0.f, beta1 = 0.f, beta2 = 0.f, omb1 = 0.f, omb2 = 0.f, eps = 0.f;
     const uint32_t* abort_word = nullptr;
     const uint32_t* wait_flags = nullptr;

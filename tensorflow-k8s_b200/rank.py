@@ -87,7 +87,7 @@ def main(argv=None) -> int:
     ap.add_argument("--workload", default="c1", help="c0 | c1 | c3 | comma-separated variable sizes")
     ap.add_argument("--optimizer", default="adam", choices=["sgd", "adam", "momentum", "ftrl"])
     ap.add_argument("--lr", type=float, default=1e-3)
-    ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level"])
+    ap.add_argument("--aggregate", default="two_level", choices=["flat", "two_level", "multimem"])
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--graph", action="store_true", help="replay each step as one CUDA graph")
     ap.add_argument("--checkpoint-dir", default=None, help="save every --save-every steps; resume from it after a restart")
