@@ -193,7 +193,7 @@ class EmbeddingTable:
         check(lib.b200ps_sparse_step(self._h, self._stream()))
 
     def capture_step(self) -> _Replay:
-        """Switches `step` to CUDA-graph replay (~25 small launches -- radix passes, scans, segments --
+        """Switches `step` to CUDA-graph replay (about ten launches -- digit counts, radix passes, segment scan, applies --
         replayed without per-launch host work; all counts live on the device and every grid is fixed,
         so the graph is valid for any ids / gradient rows written into the same buffers) and runs one
         step, which captures it.  Works across ranks too: the barriers' epoch lives in device memory."""
