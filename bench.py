@@ -122,17 +122,27 @@ def ncu_traffic(kernel: str):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons of one GPU, sampled through NVML while a timed region runs.
+
+    Every NVML query stalls its GPU for a moment -- the first queries of a process by far the most -- and with N
+    ranks in lock-step behind peer barriers a stall of any GPU is everyone's: sampling each GPU every 5 ms from the
+    first timed step on cost an 8-GPU C1 step 4-12 % (profiles/r2_n8_timeline.md).  So the thread is started
+    early (`start()` then `wait_ready()`: its first two queries are over before any timed work), `mark()` at the
+    start of a timed region drops what was seen so far and asks for one sample AT ONCE (so that even a 20-step
+    region holds one), and further samples follow every `interval` seconds."""
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
                0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
 
-    def __init__(self, device_index: int, interval: float = 0.02):
+    def __init__(self, device_index: int, interval: float = 0.01, nv=None, handle=None):
         super().__init__(daemon=True)
-        # Every NVML query stalls its GPU for a moment, and with N ranks in lock-step (peer barriers) every stall
-        # of any GPU is everyone's: at N = 8, sampling each GPU every 5 ms cost the step 4-10 % (tools/n8_variants.py:
-        # 1.20 -> 1.25-1.32 ms).  So: one sample at once, then one every `interval` seconds (0.04 s at N > 2).
         self.interval = interval
-        self.samples, self.reasons, self.max_mhz, self._halt = [], set(), None, threading.Event()
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._halt, self._wake, self._ready, self._lock = threading.Event(), threading.Event(), threading.Event(), threading.Lock()
+        self._taken = 0
         self.err = None
+        if nv is not None:  # tests hand in a stand-in for pynvml
+            self.nv, self.h = nv, handle
+            return
         try:
             import pynvml
 
@@ -151,31 +161,46 @@ class ClockSampler(threading.Thread):
 
     def run(self):
         if not self.nv:
+            self._ready.set()
             return
         while not self._halt.is_set():
             try:
-                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
                 bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception as e:
+                self.err = repr(e)
+                self._ready.set()
+                return
+            with self._lock:
+                self.samples.append(mhz)
                 for b, name in self.REASONS.items():
                     if bits & b:
                         self.reasons.add(name)
-            except Exception as e:
-                self.err = repr(e)
-                return
-            self._halt.wait(self.interval)
+            self._taken += 1
+            if self._taken >= 2:
+                self._ready.set()
+            self._wake.wait(self.interval if self._taken >= 2 else 0.0)
+            self._wake.clear()
+
+    def wait_ready(self, timeout: float = 5.0):
+        """Returns once the first two queries are done (or NVML is absent)."""
+        self._ready.wait(timeout)
+        return self
 
     def mark(self):
-        """The timed region starts here: keep only what is sampled from now on.  (The thread is started before the
-        warm-up steps because the FIRST NVML queries are the expensive ones -- with N ranks in lock-step they cost the
-        timed region 12-15 ms when the sampler was started right at its beginning.)"""
-        self.samples, self.reasons = [], set()
+        """A timed region starts here: forget what was sampled before it and take one sample now."""
+        with self._lock:
+            self.samples, self.reasons = [], set()
+        self._wake.set()
 
     def finish(self):
         self._halt.set()
+        self._wake.set()
         self.join(timeout=2)
-        s = sorted(self.samples)
-        out = {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-               "samples": len(s)}
+        with self._lock:
+            s = sorted(self.samples)
+            reasons = sorted(self.reasons)
+        out = {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(s)}
         if self.err:
             out["error"] = self.err
         return out
@@ -360,12 +385,14 @@ def sparse_measure(args, ids_kind, steps, warmup, e2e=False, cpu=False, graph=Tr
     stream = torch.cuda.Stream()
     sync()
     with torch.cuda.stream(stream):
+        sampler = ClockSampler(local, 0.01 if world <= 2 else 0.03)
+        sampler.start()
+        sampler.wait_ready()
         for _ in range(warmup):
             tab.step()
         sync()
         plan = tab.plan()
-        sampler = ClockSampler(local, 0.02 if world <= 2 else 0.04)
-        sampler.start()
+        sampler.mark()
         l0 = K.launch_count()
         launched_ms = timed(steps)
         launches = K.launch_count() - l0
@@ -644,8 +671,9 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
     stream = torch.cuda.Stream()  # a real stream: the step is ordered on it (the legacy default stream serialises)
     sync()
     with torch.cuda.stream(stream):
-        sampler = ClockSampler(local, 0.02 if world <= 2 else 0.04)
+        sampler = ClockSampler(local, 0.01 if world <= 2 else 0.03)
         sampler.start()
+        sampler.wait_ready()
         for _ in range(warmup):
             ps.step()
         sync()
@@ -779,8 +807,9 @@ def measure_dense(name, args, rank, world, local, steps, warmup, e2e=False, cpu=
                 wk.step(hx, ht)  # H2D of the mini-batches, forward/backward of the local tasks, loss D2H
                 ps.step()        # push (zero-copy) + aggregate + apply + pull (zero-copy)
 
-            smp = ClockSampler(local, 0.02 if world <= 2 else 0.04)
+            smp = ClockSampler(local, 0.01 if world <= 2 else 0.03)
             smp.start()
+            smp.wait_ready()
             n_train = args.e2e_steps or min(steps, 100)
             t_ms = timed_host_loop(train_step, lambda: None, n_train, sampler=smp)
             e2e_clocks = smp.finish()
