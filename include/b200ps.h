@@ -278,7 +278,8 @@ int b200ps_sparse_route(const float* d_grad_rows, const int64_t* d_ids, uint64_t
                         const b200ps_table_geom_t* geom, float* const* d_dst_by_gpu, void* stream);
 /* scratch for one push of n_total = W * ids_per_worker entries of a table with `dim` floats per
  * row (256-byte aligned device memory the caller owns; it holds the plan the apply call reads,
- * plus the per-chunk partial rows the apply call uses for ids with more than 256 entries) */
+ * plus the per-chunk partial rows the apply call uses for ids with more than 256 entries).
+ * sort_segment / apply take W * ids_per_worker < 2^32 - 2^16 entries (B200PS_ERR_RANGE above). */
 size_t b200ps_sparse_workspace_bytes(uint64_t n_total, int dim);
 int b200ps_sparse_sort_segment(const int64_t* const* d_ids, int W, uint64_t ids_per_worker,
                                const b200ps_table_geom_t* geom, void* d_workspace, size_t workspace_bytes,
