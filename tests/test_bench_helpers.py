@@ -69,3 +69,15 @@ def test_without_nvml_reports_the_error_and_no_numbers():
         s.mark()
         out = s.finish()
         assert out["samples"] == 0 and out["sm_mhz"] is None and "error" in out
+
+
+def test_step_form_autotune_is_a_no_op_on_one_gpu_or_when_the_form_is_given():
+    import types
+
+    for world, overlap in ((1, "auto"), (8, "on"), (8, "off")):
+        args = types.SimpleNamespace(aggregate="auto", overlap=overlap, transport="peer")
+        assert bench.tune_overlap("c1", args, 0, world) is None
+        assert not hasattr(args, "overlap_tuned")
+    # a small workload (C3: 25.6 M parameters) is never pipelined, so there is nothing to time
+    args = types.SimpleNamespace(aggregate="auto", overlap="auto", transport="peer")
+    assert bench.tune_overlap("c3", args, 0, 8) is None
