@@ -34,6 +34,9 @@
 namespace b200ps {
 namespace {
 
+// Build-time tuning knobs (-DB200PS_...) with the values measured best on B200 for C2 (2.1 M ids per push):
+// keys per thread 8 (4 / 12 / 16: within 10 %), look-back window 8 tiles (16: +9 %), 4 resident CTAs per SM
+// for the radix passes, 1024-thread CTAs for the segment scan (256 / 512: +5 / +4 %) -- profiles/r2_summary.md.
 constexpr int TILE_THREADS = 256;
 #ifndef B200PS_SWEEP_ITEMS
 #define B200PS_SWEEP_ITEMS 8
